@@ -1,0 +1,155 @@
+/*
+ * merl_b200.h -- C ABI of libmerl_b200: batched eval / pdf / sample / backward for the MERL
+ * and customized_measurment measured-BRDF plugins on NVIDIA B200 (sm_100a).
+ *
+ * What each entry point replaces.  The reference (WenCao1101/mitsuba_customization) is
+ * described only by /root/reference/README.md:1 ("Add Merl, customized_measurment brdf
+ * pluggin for Mitsuba 0.6 Mitsuba 3.0"); its plugin sources are un-vendored submodules
+ * (/root/reference/.SUBMODULES.json:8-23), so no file:line inside them can be cited.  The
+ * interfaces named below are therefore the host-renderer virtuals those plugins must
+ * override:
+ *   Mitsuba 3   BSDF::eval / pdf / eval_pdf / sample (BSDFContext, SurfaceInteraction3f,
+ *               wo in the local frame, Mask active)            -> merl_eval* / merl_pdf / merl_sample
+ *   Mitsuba 0.6 BSDF::eval / pdf / sample (BSDFSamplingRecord)  -> the *_aos entry points
+ *   plugin ctor reading `filename` (MERL .binary)              -> merl_table_create_from_file
+ *   Dr.Jit AD of the table gather (scatter_reduce)             -> merl_backward
+ *
+ * Conventions
+ *   - Every query/result pointer is a DEVICE pointer owned by the caller (a Dr.Jit
+ *     CUDAArray<float>::data(), a torch tensor's data_ptr(), a 0.6 wavefront buffer).
+ *     The library never allocates, frees or retains them.  *_host entry points take HOST
+ *     pointers instead and do their own staged copies.
+ *   - SoA: a Vector3f is three float arrays x[n], y[n], z[n] (Dr.Jit layout).
+ *     AoS: float4 per query (xyz + pad) for the 0.6 wavefront stage.
+ *   - All launches are asynchronous on `stream` (a cudaStream_t; NULL = default stream);
+ *     no hidden device synchronisation.  Table handles are immutable after creation and
+ *     may be used from any thread.
+ *   - Return 0 on success, a negative merl_status otherwise; merl_last_error() returns a
+ *     thread-local message.  No exception crosses this boundary.  There is no CPU
+ *     fallback: without a CUDA device every compute entry point fails with MERL_ERR_CUDA.
+ */
+#ifndef MERL_B200_H
+#define MERL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MERL_B200_ABI_VERSION 1
+
+typedef enum merl_status {
+    MERL_OK = 0,
+    MERL_ERR_ARG = -1,     /* NULL / misaligned / out-of-range argument */
+    MERL_ERR_IO = -2,      /* file missing, short or not MERL layout    */
+    MERL_ERR_CUDA = -3,    /* CUDA runtime error (message has details)  */
+    MERL_ERR_NOMEM = -4,
+    MERL_ERR_UNSUPPORTED = -5
+} merl_status;
+
+typedef struct merl_table merl_table_t;
+typedef void* merl_stream_t; /* cudaStream_t */
+
+/* Plugin parameters (the Properties a Mitsuba plugin would read). */
+typedef struct merl_table_params {
+    int32_t nh, nd, np;        /* table resolution; 0,0,0 = take from the file header      */
+    int32_t theta_h_sqrt;      /* 1 = MERL nonlinear theta_half bins, 0 = linear            */
+    int32_t ni;                /* sampler: incident-elevation slices, power of two <= 64    */
+    int32_t clamp_negative;    /* 1 = negative (invalid) cells evaluate to 0                */
+    int32_t cdf_nm, cdf_nq;    /* sampler CDF quadrature: sub-steps in theta_h, steps in phi_h */
+    int32_t l2_persist;        /* 1 = launches carry a persisting-L2 access window on the table */
+    int32_t reserved;
+    float cdf_floor;           /* share of solid-angle-uniform mass mixed into every row    */
+    float spec_weight;         /* probability of the tabulated half-vector lobe             */
+    double scale[3];           /* RED/GREEN/BLUE_SCALE                                      */
+} merl_table_params_t;
+
+typedef struct merl_table_info {
+    int32_t nh, nd, np, ni;
+    int32_t theta_h_sqrt, device;
+    int64_t ncell;
+    int64_t table_bytes;       /* float4 table: ncell * 16                                   */
+    const void* d_cells;       /* device float4[ncell]: the differentiable parameter         */
+    const float* d_cdf;        /* device float[ni][nh+1]                                     */
+    const float* d_dens;       /* device float[ni][nh]                                       */
+    float spec_weight;
+    int32_t smem_eval_bytes, smem_sample_bytes;
+} merl_table_info_t;
+
+/* ---- tables ---------------------------------------------------- */
+void merl_table_params_default(merl_table_params_t* p);            /* MERL: 90/90/180, scales /1500 */
+int merl_table_create_from_file(const char* path, const merl_table_params_t* p, int device,
+                                merl_table_t** out);
+/* planar_rgb: [3][nh*nd*np] doubles in .binary units (host memory). */
+int merl_table_create_from_host(const double* planar_rgb, const merl_table_params_t* p, int device,
+                                merl_table_t** out);
+int merl_table_destroy(merl_table_t* t);
+int merl_table_info(const merl_table_t* t, merl_table_info_t* out);
+/* Replace the sampler CDF (host float[ni][nh+1]); the density table is re-derived. */
+int merl_table_set_cdf(merl_table_t* t, const float* cdf_host);
+/* Copy tables back to the host; any pointer may be NULL.  Synchronous. */
+int merl_table_download(const merl_table_t* t, float* cells4_host, float* cdf_host, float* dens_host);
+
+/* ---- batched queries, SoA device pointers (rows A1-A6, A10) ----------------------------
+ * `active` may be NULL (all lanes active) or a device array of n bytes (Dr.Jit Mask).
+ * Lanes that are inactive or have wi.z <= 0 or wo.z <= 0 produce zeros. */
+int merl_bins(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+              const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
+              int32_t* idx_out, merl_stream_t stream);
+int merl_eval(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+              const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
+              float* r, float* g, float* b, merl_stream_t stream);
+int merl_pdf(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+             const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
+             float* pdf, merl_stream_t stream);
+int merl_eval_pdf(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                  const float* wox, const float* woy, const float* woz, const uint8_t* active,
+                  int64_t n, float* r, float* g, float* b, float* pdf, merl_stream_t stream);
+/* sample1 -> u1 (lobe choice), sample2 -> (u2x, u2y).  lobe: 0 = cosine, 1 = tabulated. */
+int merl_sample(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                const float* u1, const float* u2x, const float* u2y, const uint8_t* active, int64_t n,
+                float* wox, float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb,
+                uint32_t* lobe, merl_stream_t stream);
+/* grad_cells4 (device float4[ncell], caller-zeroed) += d(eval)/d(cells) . (gr, gg, gb).
+ * .w accumulates the number of contributing queries.  flags bit0: warp-aggregate equal cells
+ * with __match_any_sync before the atomic (default on; 0 = plain per-lane RED). */
+#define MERL_BWD_WARP_AGGREGATE 1u
+int merl_backward(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                  const float* wox, const float* woy, const float* woz, const float* gr,
+                  const float* gg, const float* gb, const uint8_t* active, int64_t n,
+                  float* grad_cells4, uint32_t flags, merl_stream_t stream);
+
+/* ---- AoS entry points for the Mitsuba 0.6 wavefront BSDF stage --------------------------
+ * wi4 / wo4: float4 per query (xyz, w ignored).  out4 = (r, g, b, pdf). */
+int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const float* wo4, int64_t n, float* out4,
+                      merl_stream_t stream);
+/* u4 = (u1, u2x, u2y, unused); wo4_out = (wo.xyz, pdf); weight4_out = (w.rgb, lobe as float). */
+int merl_sample_aos(const merl_table_t* t, const float* wi4, const float* u4, int64_t n, float* wo4_out,
+                    float* weight4_out, merl_stream_t stream);
+
+/* ---- host-buffer entry points (scalar-variant plugins, end-to-end timing) ---------------
+ * Same semantics as merl_eval_pdf / merl_sample but every pointer is HOST memory (pinned
+ * gives full PCIe rate).  Copies and kernels are pipelined in chunks over internal streams;
+ * returns after the results are in the host buffers. */
+int merl_eval_pdf_host(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                       const float* wox, const float* woy, const float* woz, int64_t n, float* r,
+                       float* g, float* b, float* pdf);
+int merl_sample_host(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                     const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
+                     float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe);
+
+/* ---- diagnostics ------------------------------------------------------------------------ */
+const char* merl_last_error(void);
+int merl_abi_version(void);
+/* Number of kernels this library has launched in this process (all threads). */
+int64_t merl_launch_count(void);
+/* Selects the CDF search of merl_sample: 0 = per-lane bisection, 1 = warp-cooperative
+ * ballot search.  Both give identical results; see DESIGN.md §4 for the measurements. */
+int merl_set_sample_search(int mode);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MERL_B200_H */

@@ -1,0 +1,1162 @@
+// merl_b200.cu -- libmerl_b200: C ABI (include/merl_b200.h) + sm_100a kernels.
+//
+// Kernels:  repack_kernel, cdf_build_kernel, dens_kernel (table build, one-off)
+//                          query_kernel<MODE,VEC>  (bins / eval / pdf / eval_pdf)
+//                          sample_kernel<VEC,SEARCH>, backward_kernel<VEC,AGG>
+// All query kernels are persistent grid-stride kernels sized to the SM count, stage the
+// per-table edge/density image in shared memory once per CTA, stream queries with 16-byte
+// SoA loads (evict-first) and gather one float4 per query from the L2-pinned table.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/merl_b200.h"
+#include "merl_device.cuh"
+#include "merl_slow.cuh"
+
+using namespace merl;
+
+// ------------------------------------------------------------------------------------------
+// errors, counters
+// ------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+static std::atomic<int> g_search_mode{0};
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CUDA_TRY(x)                                                                          \
+    do {                                                                                     \
+        cudaError_t e_ = (x);                                                                \
+        if (e_ != cudaSuccess)                                                               \
+            return fail(MERL_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char* merl_last_error(void) { return g_err.c_str(); }
+extern "C" int merl_abi_version(void) { return MERL_B200_ABI_VERSION; }
+extern "C" int64_t merl_launch_count(void) { return g_launches.load(); }
+extern "C" int merl_set_sample_search(int mode) {
+    if (mode != 0 && mode != 1) return fail(MERL_ERR_ARG, "sample search mode must be 0 or 1");
+    g_search_mode.store(mode);
+    return MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// host-side table object
+// ------------------------------------------------------------------------------------------
+struct merl_table {
+    TableDev dev{};
+    merl_table_params_t params{};
+    int device = 0;
+    int num_sms = 0;
+    int64_t ncell = 0;
+    float4* d_cells = nullptr;
+    float* d_image = nullptr;
+    double* d_edges64 = nullptr;   // dir_p64 | thr_h64 | thr_d64 | medge64
+    double* d_medge64 = nullptr;   // view into d_edges64
+    size_t persist_bytes = 0;      // persisting-L2 window actually granted (0 = none)
+    // host-buffer pipeline state (lazy)
+    std::mutex host_mu;
+    void* pipe = nullptr;
+};
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+extern "C" void merl_table_params_default(merl_table_params_t* p) {
+    if (!p) return;
+    memset(p, 0, sizeof *p);
+    p->nh = 90; p->nd = 90; p->np = 180;
+    p->theta_h_sqrt = 1;
+    p->ni = 32;
+    p->clamp_negative = 1;
+    p->cdf_nm = 2; p->cdf_nq = 64;
+    p->l2_persist = 1;
+    p->cdf_floor = 0.01f;
+    p->spec_weight = 0.5f;
+    p->scale[0] = 1.0 / 1500.0; p->scale[1] = 1.15 / 1500.0; p->scale[2] = 1.66 / 1500.0;
+}
+
+// ------------------------------------------------------------------------------------------
+// table-build kernels
+// ------------------------------------------------------------------------------------------
+// Planar double RGB (file layout) -> channel-interleaved float4, prescaled by the channel
+// scales, negatives clamped.  .w keeps one validity bit per channel (raw >= 0) as a float.
+__global__ void repack_kernel(const double* __restrict__ raw, int64_t ncell, double s0, double s1,
+                              double s2, int clamp_negative, float4* __restrict__ cells) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ncell;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        double v0 = raw[i] * s0, v1 = raw[i + ncell] * s1, v2 = raw[i + 2 * ncell] * s2;
+        int bits = (v0 >= 0.0) | ((v1 >= 0.0) << 1) | ((v2 >= 0.0) << 2);
+        if (clamp_negative) { v0 = fmax(v0, 0.0); v1 = fmax(v1, 0.0); v2 = fmax(v2, 0.0); }
+        else bits = 7;
+        cells[i] = make_float4((float)v0, (float)v1, (float)v2, (float)bits);
+    }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Row CDFs of the tabulated half-vector lobe (the oracle's orc_build_cdf states
+// the same quadrature).  One CTA per incident slice j; warp w integrates bins w, w+W, ...
+__global__ void __launch_bounds__(256) cdf_build_kernel(TableDev t, const double* __restrict__ medge,
+                                                        int nm, int nq, double floor_frac,
+                                                        float* __restrict__ cdf_out) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    stage_image(t, smem, t.off_dens);
+    const SmemView v = make_view(t, smem);
+    double* W = reinterpret_cast<double*>(smem + ((t.off_dens + 3) & ~3));
+    const int j = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    const double c0 = (j + 0.5) / t.ni;
+    const float ax = (float)sqrt(1.0 - c0 * c0), ay = 0.f, az = (float)c0;
+    const double PI = 3.14159265358979323846;
+    for (int i = warp; i < t.nh; i += nwarp) {
+        double acc = 0.0;
+        for (int s = lane; s < nm * nq; s += 32) {
+            const int m = s / nq, q = s - m * nq;
+            const double mm = medge[i] + (m + 0.5) / nm * (medge[i + 1] - medge[i]);
+            const double ct = 1.0 - mm, st = sqrt(mm * (2.0 - mm));
+            double sp, cp;
+            sincos(2.0 * PI * (q + 0.5) / nq, &sp, &cp);
+            const double hx = st * cp, hy = st * sp, hz = ct;
+            const double c = (double)ax * hx + (double)az * hz;
+            if (!(c > 0.0)) continue;
+            const float bx = (float)(2.0 * c * hx - ax), by = (float)(2.0 * c * hy - ay),
+                        bz = (float)(2.0 * c * hz - az);
+            if (!(bz > 0.f)) continue;
+            const HalfDiff h = half_diff_setup(ax, ay, az, bx, by, bz);
+            const Bins b = compute_bins(t, v, ax, ay, az, bx, by, bz, h);
+            const float4 cell = __ldg(&t.cells[(b.ih * t.nd + b.id) * t.np + b.ip]);
+            const double lum = 0.2126 * (double)(cell.x * bz) + 0.7152 * (double)(cell.y * bz) +
+                               0.0722 * (double)(cell.z * bz);
+            acc += lum * 4.0 * c;
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) W[i] = acc / (nm * nq) * 2.0 * PI * (medge[i + 1] - medge[i]);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double total = 0.0;
+        for (int i = 0; i < t.nh; ++i) total += W[i];
+        const double msum = medge[t.nh] - medge[0];
+        float* row = cdf_out + (size_t)j * (t.nh + 1);
+        double run = 0.0;
+        row[0] = 0.f;
+        for (int i = 0; i < t.nh; ++i) {
+            const double uni = (medge[i + 1] - medge[i]) / msum;
+            const double P = total > 0.0 ? (1.0 - floor_frac) * W[i] / total + floor_frac * uni : uni;
+            run += P;
+            row[i + 1] = (float)(run > 1.0 ? 1.0 : run);
+        }
+        row[t.nh] = 1.f;
+    }
+}
+
+// dens[j][i] = P_ji / (8 pi (M_{i+1}-M_i)) with P_ji the fp32 CDF's own increment, so that
+// pdf() integrates to exactly what sample() draws.
+__global__ void dens_kernel(const float* __restrict__ cdf, const double* __restrict__ medge, int ni,
+                            int nh, float* __restrict__ dens) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= ni * nh) return;
+    const int j = k / nh, i = k - j * nh;
+    const double P = (double)cdf[j * (nh + 1) + i + 1] - (double)cdf[j * (nh + 1) + i];
+    dens[k] = (float)(P / (8.0 * 3.14159265358979323846 * (medge[i + 1] - medge[i])));
+}
+
+// ------------------------------------------------------------------------------------------
+// streamed SoA access: VEC consecutive queries per thread, 16-byte evict-first transactions
+// ------------------------------------------------------------------------------------------
+template <int VEC> struct Pack { float v[VEC]; };
+
+template <int VEC> __device__ __forceinline__ Pack<VEC> load_stream(const float* p, int64_t g);
+template <> __device__ __forceinline__ Pack<1> load_stream<1>(const float* p, int64_t g) {
+    Pack<1> r; r.v[0] = __ldcs(p + g); return r;
+}
+template <> __device__ __forceinline__ Pack<4> load_stream<4>(const float* p, int64_t g) {
+    const float4 f = __ldcs(reinterpret_cast<const float4*>(p) + g);
+    Pack<4> r; r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w; return r;
+}
+template <int VEC> __device__ __forceinline__ void store_stream(float* p, int64_t g, const Pack<VEC>& a);
+template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g, const Pack<1>& a) {
+    __stcs(p + g, a.v[0]);
+}
+template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g, const Pack<4>& a) {
+    __stcs(reinterpret_cast<float4*>(p) + g, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
+}
+template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
+template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
+    return p ? (p[g] != 0) : 1u;
+}
+template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p, int64_t g) {
+    if (!p) return 0xFu;
+    const uint32_t w = __ldcs(reinterpret_cast<const uint32_t*>(p) + g);
+    return ((w & 0xFFu) != 0) | (((w >> 8) & 0xFFu) != 0) << 1 | (((w >> 16) & 0xFFu) != 0) << 2 |
+           ((w >> 24) != 0) << 3;
+}
+
+struct QueryIn {
+    const float *wix, *wiy, *wiz, *wox, *woy, *woz;
+    const uint8_t* active;
+};
+
+// pdf of the two-lobe sampler given the bins (row A5; oracle: eval_pdf_one).
+__device__ __forceinline__ float pdf_from_bins(const TableDev& t, const SmemView& v, float az, float bz,
+                                               const HalfDiff& h, int ih) {
+    const int j = min((int)(az * (float)t.ni), t.ni - 1);
+    float p = (1.f - t.spec_weight) * bz * 0.318309886f;
+    if (h.A > 0.f) p = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
+    return p;
+}
+
+// ------------------------------------------------------------------------------------------
+// bins / eval / pdf / eval_pdf   (rows A1-A5)
+// ------------------------------------------------------------------------------------------
+enum QueryMode { MODE_BINS = 0, MODE_EVAL = 1, MODE_PDF = 2, MODE_EVAL_PDF = 3 };
+
+struct QueryOut {
+    float *r, *g, *b, *pdf;
+    int32_t* idx;
+};
+
+template <int MODE, int VEC>
+__global__ void __launch_bounds__(256) query_kernel(const TableDev t, const QueryIn in, const int64_t ngroups,
+                                                    const QueryOut out) {
+    constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
+    constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    stage_image(t, smem, kPdf ? t.image_eval_floats : t.off_dens);
+    const SmemView v = make_view(t, smem);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < ngroups; g += stride) {
+        const Pack<VEC> ax = load_stream<VEC>(in.wix, g), ay = load_stream<VEC>(in.wiy, g),
+                        az = load_stream<VEC>(in.wiz, g), bx = load_stream<VEC>(in.wox, g),
+                        by = load_stream<VEC>(in.woy, g), bz = load_stream<VEC>(in.woz, g);
+        const unsigned act = load_active<VEC>(in.active, g);
+        int idx[VEC];
+        Pack<VEC> pdf;
+        bool valid[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
+            const Bins b = compute_bins(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h);
+            idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
+            if (kPdf) pdf.v[q] = valid[q] ? pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih) : 0.f;
+        }
+        if (kEval) {
+            float4 cell[VEC];
+#pragma unroll
+            for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
+            Pack<VEC> r, gg, bb;
+#pragma unroll
+            for (int q = 0; q < VEC; ++q) {
+                const float c = valid[q] ? bz.v[q] : 0.f;
+                r.v[q] = cell[q].x * c; gg.v[q] = cell[q].y * c; bb.v[q] = cell[q].z * c;
+            }
+            store_stream<VEC>(out.r, g, r);
+            store_stream<VEC>(out.g, g, gg);
+            store_stream<VEC>(out.b, g, bb);
+        }
+        if (kPdf) store_stream<VEC>(out.pdf, g, pdf);
+        if (MODE == MODE_BINS) {
+#pragma unroll
+            for (int q = 0; q < VEC; ++q) out.idx[g * VEC + q] = valid[q] ? idx[q] : -1;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// sample   (row A6; oracle: draw_direction + eval_pdf_one)
+// ------------------------------------------------------------------------------------------
+// Mitsuba 3's concentric square->disk map, lifted to the cosine-weighted hemisphere.
+__device__ __forceinline__ void cosine_hemisphere(float ux, float uy, float& x, float& y, float& z) {
+    const float sx = fmaf(2.f, ux, -1.f), sy = fmaf(2.f, uy, -1.f);
+    const bool q13 = fabsf(sx) < fabsf(sy);
+    const float r = q13 ? sy : sx, rp = q13 ? sx : sy;
+    float ph = 0.25f * __fdividef(rp, r);            // in units of pi
+    if (q13) ph = 0.5f - ph;
+    if (sx == 0.f && sy == 0.f) ph = 0.f;
+    float s, c;
+    sincospif(ph, &s, &c);
+    x = r * c; y = r * s;
+    z = sqrtf(fmaxf(0.f, 1.f - x * x - y * y));
+}
+
+// Largest i in [0, nh-1] with row[i] <= u: per-lane bisection over the smem-resident row.
+__device__ __forceinline__ int search_lane(const float* row, int nh, float u) {
+    int lo = 0, hi = nh;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (row[mid] <= u) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+// Same result, warp-cooperative: the warp walks its 32 queries; for each, every lane tests a
+// strided share of the row (conflict-free LDS) and __ballot_sync/__popc count the entries <= u.
+// row[] is non-decreasing, so that count - 1 is the bisection's answer.
+__device__ __forceinline__ int search_warp_coop(const float* cdf, int nh, int my_row, float my_u,
+                                                bool my_need, unsigned lane) {
+    int result = 0;
+    unsigned todo = __ballot_sync(0xffffffffu, my_need);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int row_i = __shfl_sync(0xffffffffu, my_row, src);
+        const float u = __shfl_sync(0xffffffffu, my_u, src);
+        const float* row = cdf + row_i * (nh + 1);
+        int count = 0;
+        for (int base = 0; base < nh; base += 32) {   // entries 0..nh-1 (row[nh] = 1 > u always)
+            const int e = base + (int)lane;
+            const bool le = (e < nh) && (row[e] <= u);
+            count += __popc(__ballot_sync(0xffffffffu, le));
+        }
+        if ((int)lane == src) result = max(count - 1, 0);
+    }
+    return result;
+}
+
+struct SampleIn {
+    const float *wix, *wiy, *wiz, *u1, *u2x, *u2y;
+    const uint8_t* active;
+};
+struct SampleOut {
+    float *wox, *woy, *woz, *pdf, *wr, *wg, *wb;
+    uint32_t* lobe;
+};
+
+template <int VEC, int SEARCH>
+__global__ void __launch_bounds__(256) sample_kernel(const TableDev t, const SampleIn in, const int64_t ngroups,
+                                                     const SampleOut out) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    stage_image(t, smem, t.image_full_floats);
+    const SmemView v = make_view(t, smem);
+    const unsigned lane = threadIdx.x & 31u;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // SEARCH==1 uses warp collectives inside the loop, so the trip count must be warp-uniform.
+    const int64_t g0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t gend = SEARCH ? ((ngroups + 31) / 32) * 32 : ngroups;
+    for (int64_t g = g0; g < gend; g += stride) {
+        const bool in_range = g < ngroups;
+        const int64_t gl = in_range ? g : 0;
+        const Pack<VEC> ax = load_stream<VEC>(in.wix, gl), ay = load_stream<VEC>(in.wiy, gl),
+                        az = load_stream<VEC>(in.wiz, gl), u1 = load_stream<VEC>(in.u1, gl),
+                        ux = load_stream<VEC>(in.u2x, gl), uy = load_stream<VEC>(in.u2y, gl);
+        const unsigned act = in_range ? load_active<VEC>(in.active, gl) : 0u;
+        Pack<VEC> bx, by, bz, pdf, wr, wg, wb;
+        uint32_t lobe[VEC];
+        int idx[VEC];
+        bool valid[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            const bool ok = ((act >> q) & 1u) && az.v[q] > 0.f;
+            const bool spec = u1.v[q] < t.spec_weight;
+            lobe[q] = (ok && spec) ? 1u : 0u;
+            float x, y, z;
+            cosine_hemisphere(ux.v[q], uy.v[q], x, y, z);
+            const int j = max(min((int)(az.v[q] * (float)t.ni), t.ni - 1), 0);
+            int i;
+            if (SEARCH) i = search_warp_coop(v.cdf, t.nh, j, ux.v[q], ok && spec, lane);
+            else i = spec ? search_lane(v.cdf + j * (t.nh + 1), t.nh, ux.v[q]) : 0;
+            if (spec) {
+                const float* row = v.cdf + j * (t.nh + 1);
+                const float c0 = row[i], c1 = row[i + 1];
+                const float w = c1 - c0;
+                const float f = w > 0.f ? __fdividef(ux.v[q] - c0, w) : 0.5f;
+                const float m0 = v.medge[i], m1 = v.medge[i + 1];
+                const float m = fmaf(f, m1 - m0, m0);
+                const float ct = 1.f - m, st = sqrtf(m * (2.f - m));
+                float sp, cp;
+                sincospif(2.f * uy.v[q], &sp, &cp);
+                const float hx = st * cp, hy = st * sp, hz = ct;
+                const float c2 = 2.f * fmaf(ax.v[q], hx, fmaf(ay.v[q], hy, az.v[q] * hz));
+                x = fmaf(c2, hx, -ax.v[q]); y = fmaf(c2, hy, -ay.v[q]); z = fmaf(c2, hz, -az.v[q]);
+            }
+            bx.v[q] = x; by.v[q] = y; bz.v[q] = z;
+            valid[q] = ok && z > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], x, y, z);
+            const Bins b = compute_bins(t, v, ax.v[q], ay.v[q], az.v[q], x, y, z, h);
+            idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
+            pdf.v[q] = valid[q] ? pdf_from_bins(t, v, az.v[q], z, h, b.ih) : 0.f;
+            if (!ok) { bx.v[q] = 0.f; by.v[q] = 0.f; bz.v[q] = 0.f; }
+        }
+        float4 cell[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            const bool good = valid[q] && pdf.v[q] > 0.f;
+            const float s = good ? __fdividef(bz.v[q], pdf.v[q]) : 0.f;
+            wr.v[q] = cell[q].x * s; wg.v[q] = cell[q].y * s; wb.v[q] = cell[q].z * s;
+            if (!good) pdf.v[q] = 0.f;
+        }
+        if (in_range) {
+            store_stream<VEC>(out.wox, g, bx); store_stream<VEC>(out.woy, g, by); store_stream<VEC>(out.woz, g, bz);
+            store_stream<VEC>(out.pdf, g, pdf);
+            store_stream<VEC>(out.wr, g, wr); store_stream<VEC>(out.wg, g, wg); store_stream<VEC>(out.wb, g, wb);
+            if (VEC == 4) {
+                reinterpret_cast<uint4*>(out.lobe)[g] = make_uint4(lobe[0], lobe[VEC > 1 ? 1 : 0],
+                                                                  lobe[VEC > 2 ? 2 : 0], lobe[VEC > 3 ? 3 : 0]);
+            } else {
+                out.lobe[g] = lobe[0];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward   (row A10): grad_cells[idx] += (g_r, g_g, g_b) * cos(theta_o), one 16-byte RED
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+struct BackwardIn {
+    QueryIn q;
+    const float *gr, *gg, *gb;
+};
+
+template <int VEC, int AGG>
+__global__ void __launch_bounds__(256) backward_kernel(const TableDev t, const BackwardIn in, const int64_t ngroups,
+                                                       float4* __restrict__ grad) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    stage_image(t, smem, t.off_dens);
+    const SmemView v = make_view(t, smem);
+    const unsigned lane = threadIdx.x & 31u;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t g0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t gend = AGG ? ((ngroups + 31) / 32) * 32 : ngroups;
+    for (int64_t g = g0; g < gend; g += stride) {
+        const bool in_range = g < ngroups;
+        const int64_t gl = in_range ? g : 0;
+        const Pack<VEC> ax = load_stream<VEC>(in.q.wix, gl), ay = load_stream<VEC>(in.q.wiy, gl),
+                        az = load_stream<VEC>(in.q.wiz, gl), bx = load_stream<VEC>(in.q.wox, gl),
+                        by = load_stream<VEC>(in.q.woy, gl), bz = load_stream<VEC>(in.q.woz, gl),
+                        gr = load_stream<VEC>(in.gr, gl), gg = load_stream<VEC>(in.gg, gl),
+                        gb = load_stream<VEC>(in.gb, gl);
+        const unsigned act = in_range ? load_active<VEC>(in.q.active, gl) : 0u;
+        int idx[VEC];
+        bool valid[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
+            const Bins b = compute_bins(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h);
+            idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
+        }
+        float bits[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) bits[q] = __ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx[q] + 3]);
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            const int m = (int)bits[q];
+            const float c = valid[q] ? bz.v[q] : 0.f;
+            float v0 = (m & 1) ? gr.v[q] * c : 0.f, v1 = (m & 2) ? gg.v[q] * c : 0.f,
+                  v2 = (m & 4) ? gb.v[q] * c : 0.f, v3 = valid[q] ? 1.f : 0.f;
+            bool emit = valid[q];
+            if (AGG) {
+                // lanes of this warp that hit the same cell fold into the lowest such lane
+                const int key = valid[q] ? idx[q] : -1 - (int)lane;
+                const unsigned peers = __match_any_sync(0xffffffffu, key);
+                if (__any_sync(0xffffffffu, peers & (peers - 1))) {
+                    if (peers == 0xffffffffu) {      // whole warp on one cell: butterfly
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+                            v2 += __shfl_xor_sync(0xffffffffu, v2, o); v3 += __shfl_xor_sync(0xffffffffu, v3, o);
+                        }
+                        emit = emit && lane == 0;
+                    } else {
+                        const bool leader = (int)lane == __ffs(peers) - 1;
+                        unsigned rest = leader ? (peers & ~(1u << lane)) : 0u;
+                        const float m0 = v0, m1 = v1, m2 = v2, m3 = v3;
+                        while (__any_sync(0xffffffffu, rest != 0u)) {
+                            const int src = rest ? __ffs(rest) - 1 : (int)lane;
+                            const float a0 = __shfl_sync(0xffffffffu, m0, src), a1 = __shfl_sync(0xffffffffu, m1, src),
+                                        a2 = __shfl_sync(0xffffffffu, m2, src), a3 = __shfl_sync(0xffffffffu, m3, src);
+                            if (rest) { v0 += a0; v1 += a1; v2 += a2; v3 += a3; rest &= rest - 1; }
+                        }
+                        emit = emit && leader;
+                    }
+                }
+            }
+            if (emit) red_add_v4(grad + idx[q], v0, v1, v2, v3);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// AoS variants for the Mitsuba 0.6 wavefront BSDF stage (float4 per query)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) eval_pdf_aos_kernel(const TableDev t, const float4* __restrict__ wi4,
+                                                           const float4* __restrict__ wo4, const int64_t n,
+                                                           float4* __restrict__ out4) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    stage_image(t, smem, t.image_eval_floats);
+    const SmemView v = make_view(t, smem);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n; g += stride) {
+        const float4 a = __ldcs(wi4 + g), b = __ldcs(wo4 + g);
+        const bool valid = a.z > 0.f && b.z > 0.f;
+        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, b.x, b.y, b.z);
+        const Bins bn = compute_bins(t, v, a.x, a.y, a.z, b.x, b.y, b.z, h);
+        const float4 cell = __ldg(&t.cells[(bn.ih * t.nd + bn.id) * t.np + bn.ip]);
+        const float c = valid ? b.z : 0.f;
+        const float p = valid ? pdf_from_bins(t, v, a.z, b.z, h, bn.ih) : 0.f;
+        __stcs(out4 + g, make_float4(cell.x * c, cell.y * c, cell.z * c, p));
+    }
+}
+
+__global__ void __launch_bounds__(256) sample_aos_kernel(const TableDev t, const float4* __restrict__ wi4,
+                                                         const float4* __restrict__ u4, const int64_t n,
+                                                         float4* __restrict__ wo4, float4* __restrict__ w4) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    stage_image(t, smem, t.image_full_floats);
+    const SmemView v = make_view(t, smem);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n; g += stride) {
+        const float4 a = __ldcs(wi4 + g), u = __ldcs(u4 + g);
+        const bool ok = a.z > 0.f;
+        const bool spec = u.x < t.spec_weight;
+        float x, y, z;
+        cosine_hemisphere(u.y, u.z, x, y, z);
+        if (spec) {
+            const int j = max(min((int)(a.z * (float)t.ni), t.ni - 1), 0);
+            const float* row = v.cdf + j * (t.nh + 1);
+            const int i = search_lane(row, t.nh, u.y);
+            const float c0 = row[i], w = row[i + 1] - c0;
+            const float f = w > 0.f ? __fdividef(u.y - c0, w) : 0.5f;
+            const float m0 = v.medge[i], m = fmaf(f, v.medge[i + 1] - m0, m0);
+            const float ct = 1.f - m, st = sqrtf(m * (2.f - m));
+            float sp, cp;
+            sincospif(2.f * u.z, &sp, &cp);
+            const float hx = st * cp, hy = st * sp, hz = ct;
+            const float c2 = 2.f * fmaf(a.x, hx, fmaf(a.y, hy, a.z * hz));
+            x = fmaf(c2, hx, -a.x); y = fmaf(c2, hy, -a.y); z = fmaf(c2, hz, -a.z);
+        }
+        const bool valid = ok && z > 0.f;
+        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, x, y, z);
+        const Bins bn = compute_bins(t, v, a.x, a.y, a.z, x, y, z, h);
+        const float4 cell = __ldg(&t.cells[(bn.ih * t.nd + bn.id) * t.np + bn.ip]);
+        float p = valid ? pdf_from_bins(t, v, a.z, z, h, bn.ih) : 0.f;
+        const bool good = valid && p > 0.f;
+        const float s = good ? __fdividef(z, p) : 0.f;
+        if (!good) p = 0.f;
+        if (!ok) { x = 0.f; y = 0.f; z = 0.f; }
+        __stcs(wo4 + g, make_float4(x, y, z, p));
+        __stcs(w4 + g, make_float4(cell.x * s, cell.y * s, cell.z * s, (ok && spec) ? 1.f : 0.f));
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host: launch plumbing
+// ------------------------------------------------------------------------------------------
+static constexpr int kThreads = 256;
+static constexpr size_t kMaxSmemBytes = 100 * 1024;
+
+template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
+    // cached per (kernel instantiation, smem size)
+    static std::mutex mu;
+    static std::vector<std::pair<std::pair<const void*, size_t>, int>> cache;
+    std::lock_guard<std::mutex> lk(mu);
+    const std::pair<const void*, size_t> key((const void*)kernel, smem);
+    for (auto& e : cache)
+        if (e.first == key) return e.second;
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmemBytes);
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kThreads, smem) != cudaSuccess || nb < 1) nb = 1;
+    cache.push_back({key, nb});
+    return nb;
+}
+
+// Persistent launch: grid = min(work, SMs x resident CTAs), with the table's persisting-L2
+// access window attached to the launch itself (no mutation of the caller's stream).
+template <typename K, typename... Args>
+static int launch_persistent(const merl_table* t, K kernel, size_t smem, int64_t items, cudaStream_t stream,
+                             Args... args) {
+    if (items <= 0) return MERL_OK;
+    const int64_t want = (items + kThreads - 1) / kThreads;
+    const int64_t cap = (int64_t)t->num_sms * blocks_per_sm(kernel, smem);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(want < cap ? want : cap));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (t->persist_bytes) {
+        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[0].val.accessPolicyWindow.base_ptr = (void*)t->d_cells;
+        attr[0].val.accessPolicyWindow.num_bytes = t->persist_bytes;
+        attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
+        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    }
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, args...));
+    g_launches.fetch_add(1);
+    return MERL_OK;
+}
+
+static inline bool aligned(const void* p, size_t a) { return p == nullptr || ((uintptr_t)p % a) == 0; }
+static inline size_t eval_smem(const merl_table* t, bool pdf) {
+    return (size_t)(((pdf ? t->dev.image_eval_floats : t->dev.off_dens) + 3) & ~3) * sizeof(float);
+}
+static inline size_t full_smem(const merl_table* t) {
+    return (size_t)((t->dev.image_full_floats + 3) & ~3) * sizeof(float);
+}
+
+static QueryIn offset_in(QueryIn q, int64_t o) {
+    q.wix += o; q.wiy += o; q.wiz += o; q.wox += o; q.woy += o; q.woz += o;
+    if (q.active) q.active += o;
+    return q;
+}
+static QueryOut offset_out(QueryOut q, int64_t o) {
+    if (q.r) q.r += o; if (q.g) q.g += o; if (q.b) q.b += o; if (q.pdf) q.pdf += o; if (q.idx) q.idx += o;
+    return q;
+}
+
+template <int MODE>
+static int run_query_mode(const merl_table* t, const QueryIn& in, int64_t n, const QueryOut& out, cudaStream_t s) {
+    const size_t smem = eval_smem(t, MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
+    const bool vec = aligned(in.wix, 16) && aligned(in.wiy, 16) && aligned(in.wiz, 16) && aligned(in.wox, 16) &&
+                     aligned(in.woy, 16) && aligned(in.woz, 16) && aligned(in.active, 4) && aligned(out.r, 16) &&
+                     aligned(out.g, 16) && aligned(out.b, 16) && aligned(out.pdf, 16) && aligned(out.idx, 16);
+    int64_t done = 0;
+    if (vec && n >= 4) {
+        const int rc = launch_persistent(t, query_kernel<MODE, 4>, smem, n / 4, s, t->dev, in, n / 4, out);
+        if (rc) return rc;
+        done = (n / 4) * 4;
+    }
+    if (done < n)
+        return launch_persistent(t, query_kernel<MODE, 1>, smem, n - done, s, t->dev, offset_in(in, done), n - done,
+                                 offset_out(out, done));
+    return MERL_OK;
+}
+
+static int check_query_args(const merl_table* t, const float* a, const float* b, const float* c, const float* d,
+                            const float* e, const float* f, int64_t n) {
+    if (!t) return fail(MERL_ERR_ARG, "table handle is NULL");
+    if (n < 0) return fail(MERL_ERR_ARG, "n must be >= 0");
+    if (n > 0 && (!a || !b || !c || !d || !e || !f)) return fail(MERL_ERR_ARG, "query pointer is NULL");
+    return MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// host: table creation (rows A3, A8)
+// ------------------------------------------------------------------------------------------
+static bool is_pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
+static int round4(int x) { return (x + 3) & ~3; }
+
+static int upload_sampler(merl_table* t, const float* cdf_host, cudaStream_t s) {
+    // cdf_host == NULL: build on the device from the table; otherwise install the given rows.
+    const TableDev& d = t->dev;
+    float* d_cdf = t->d_image + d.off_cdf;
+    if (cdf_host) {
+        CUDA_TRY(cudaMemcpyAsync(d_cdf, cdf_host, sizeof(float) * d.ni * (d.nh + 1), cudaMemcpyHostToDevice, s));
+    } else {
+        const size_t smem = (size_t)round4(d.off_dens) * sizeof(float) + sizeof(double) * d.nh;
+        cudaFuncSetAttribute(cdf_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmemBytes);
+        cdf_build_kernel<<<d.ni, kThreads, smem, s>>>(d, t->d_medge64, t->params.cdf_nm, t->params.cdf_nq,
+                                                     (double)t->params.cdf_floor, d_cdf);
+        CUDA_TRY(cudaGetLastError());
+        g_launches.fetch_add(1);
+    }
+    const int nd = d.ni * d.nh;
+    dens_kernel<<<(nd + 255) / 256, 256, 0, s>>>(d_cdf, t->d_medge64, d.ni, d.nh, t->d_image + d.off_dens);
+    CUDA_TRY(cudaGetLastError());
+    g_launches.fetch_add(1);
+    return MERL_OK;
+}
+
+static void free_table(merl_table* t) {
+    if (!t) return;
+    DeviceGuard g(t->device);
+    cudaFree(t->d_cells);
+    cudaFree(t->d_image);
+    cudaFree(t->d_edges64);
+    delete t;
+}
+
+static void free_pipe(merl_table* t);
+
+static int build_table(const double* planar, const merl_table_params_t* pin, int device, merl_table_t** out) {
+    if (!planar || !out) return fail(MERL_ERR_ARG, "NULL argument");
+    merl_table_params_t p;
+    if (pin) p = *pin; else merl_table_params_default(&p);
+    if (p.nh < 2 || p.nh > kMaxNH || p.nd < 2 || p.nd > kMaxND || p.np < 2 || p.np > kMaxNP)
+        return fail(MERL_ERR_UNSUPPORTED, "resolution %dx%dx%d outside [2..%d]x[2..%d]x[2..%d]", p.nh, p.nd, p.np,
+                    kMaxNH, kMaxND, kMaxNP);
+    if (!is_pow2(p.ni) || p.ni > kMaxNI) return fail(MERL_ERR_ARG, "ni must be a power of two <= %d", kMaxNI);
+    if (!(p.spec_weight >= 0.f && p.spec_weight <= 1.f)) return fail(MERL_ERR_ARG, "spec_weight outside [0,1]");
+    if (p.cdf_nm < 1 || p.cdf_nq < 1) return fail(MERL_ERR_ARG, "cdf quadrature orders must be >= 1");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(MERL_ERR_ARG, "device %d not in [0,%d)", device, ndev);
+    DeviceGuard guard(device);
+
+    merl_table* t = new merl_table();
+    t->params = p;
+    t->device = device;
+    t->ncell = (int64_t)p.nh * p.nd * p.np;
+    cudaDeviceGetAttribute(&t->num_sms, cudaDevAttrMultiProcessorCount, device);
+    TableDev& d = t->dev;
+    d.nh = p.nh; d.nd = p.nd; d.np = p.np; d.ni = p.ni; d.theta_h_sqrt = p.theta_h_sqrt;
+    d.off_thr_d = round4(p.nh + 1);
+    d.off_dir_p = d.off_thr_d + round4(p.nd + 1);
+    d.off_dens = d.off_dir_p + round4(2 * (p.np + 1));
+    d.off_cdf = d.off_dens + round4(p.ni * p.nh);
+    d.off_medge = d.off_cdf + round4(p.ni * (p.nh + 1));
+    d.image_eval_floats = d.off_dens + p.ni * p.nh;
+    d.image_full_floats = d.off_medge + p.nh + 1;
+    if ((size_t)round4(d.image_full_floats) * sizeof(float) > kMaxSmemBytes) {
+        const int need = d.image_full_floats;
+        delete t;
+        return fail(MERL_ERR_UNSUPPORTED, "sampler tables (%d floats) exceed the %zu-byte shared-memory image", need,
+                    kMaxSmemBytes);
+    }
+    const double PI = 3.14159265358979323846;
+    d.kh = (float)(p.theta_h_sqrt ? (double)p.nh * p.nh * 2.0 / PI : p.nh * 2.0 / PI);
+    d.kd = (float)(p.nd * 2.0 / PI);
+    d.kp = (float)(p.np / PI);
+    d.spec_weight = p.spec_weight;
+
+    // bin edges in double (host libm), then rounded to fp32 for tier 1
+    const int n64 = (p.nh + 1) + (p.nd + 1) + 2 * (p.np + 1) + (p.nh + 1);
+    std::vector<double> e64(n64);
+    double* dir_p = e64.data();                 // first: double2 loads need 16-byte alignment
+    double* thr_h = dir_p + 2 * (p.np + 1);
+    double* thr_d = thr_h + p.nh + 1;
+    double* medge = thr_d + p.nd + 1;
+    for (int i = 0; i <= p.nh; ++i) {
+        const double u = (double)i / p.nh;
+        const double th = (PI / 2.0) * (p.theta_h_sqrt ? u * u : u);
+        const double tn = tan(th);
+        thr_h[i] = (i == 0) ? 0.0 : (i == p.nh ? INFINITY : tn * tn);
+        const double sh = sin(0.5 * th);
+        medge[i] = 2.0 * sh * sh;
+    }
+    for (int k = 0; k <= p.nd; ++k) {
+        const double c = cos((double)k / p.nd * (PI / 2.0));
+        thr_d[k] = (k == 0) ? 4.0 : (k == p.nd ? -4.0 : c * c);
+    }
+    for (int k = 0; k <= p.np; ++k) {
+        const double a = (double)k / p.np * PI;
+        dir_p[2 * k] = (k == 0) ? 1.0 : (k == p.np ? -1.0 : cos(a));
+        dir_p[2 * k + 1] = (k == 0 || k == p.np) ? 0.0 : sin(a);
+    }
+    std::vector<float> img(round4(d.image_full_floats), 0.f);
+    for (int i = 0; i <= p.nh; ++i) { img[i] = (float)thr_h[i]; img[d.off_medge + i] = (float)medge[i]; }
+    for (int k = 0; k <= p.nd; ++k) img[d.off_thr_d + k] = (float)thr_d[k];
+    for (int k = 0; k < 2 * (p.np + 1); ++k) img[d.off_dir_p + k] = (float)dir_p[k];
+
+    cudaStream_t s = nullptr;
+    double* d_raw = nullptr;
+    int rc = MERL_OK;
+    auto bail = [&](int code) { cudaFree(d_raw); free_table(t); return code; };
+#define TRY_OR_BAIL(x)                                                                            \
+    do {                                                                                          \
+        cudaError_t e_ = (x);                                                                     \
+        if (e_ != cudaSuccess)                                                                    \
+            return bail(fail(MERL_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__)); \
+    } while (0)
+    TRY_OR_BAIL(cudaMalloc(&t->d_cells, sizeof(float4) * t->ncell));
+    TRY_OR_BAIL(cudaMalloc(&t->d_image, sizeof(float) * img.size()));
+    TRY_OR_BAIL(cudaMalloc(&t->d_edges64, sizeof(double) * n64));
+    TRY_OR_BAIL(cudaMalloc(&d_raw, sizeof(double) * 3 * t->ncell));
+    TRY_OR_BAIL(cudaMemcpyAsync(d_raw, planar, sizeof(double) * 3 * t->ncell, cudaMemcpyHostToDevice, s));
+    TRY_OR_BAIL(cudaMemcpyAsync(t->d_image, img.data(), sizeof(float) * img.size(), cudaMemcpyHostToDevice, s));
+    TRY_OR_BAIL(cudaMemcpyAsync(t->d_edges64, e64.data(), sizeof(double) * n64, cudaMemcpyHostToDevice, s));
+    d.cells = t->d_cells;
+    d.image = t->d_image;
+    d.dir_p64 = reinterpret_cast<const double2*>(t->d_edges64);
+    d.thr_h64 = t->d_edges64 + 2 * (p.np + 1);
+    d.thr_d64 = d.thr_h64 + p.nh + 1;
+    t->d_medge64 = const_cast<double*>(d.thr_d64) + p.nd + 1;
+    repack_kernel<<<t->num_sms * 4, 256, 0, s>>>(d_raw, t->ncell, p.scale[0], p.scale[1], p.scale[2],
+                                                 p.clamp_negative, t->d_cells);
+    TRY_OR_BAIL(cudaGetLastError());
+    g_launches.fetch_add(1);
+    rc = upload_sampler(t, nullptr, s);
+    if (rc) return bail(rc);
+    TRY_OR_BAIL(cudaStreamSynchronize(s));
+    cudaFree(d_raw);
+    d_raw = nullptr;
+
+    // L2 persistence (BASELINE.json: "pinned in L2 with a cudaAccessPolicyWindow")
+    if (p.l2_persist) {
+        int max_persist = 0, max_window = 0;
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, device);
+        size_t want = sizeof(float4) * (size_t)t->ncell;
+        size_t cur = 0;
+        cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+        if (max_persist > 0 && max_window > 0) {
+            const size_t lim = want < (size_t)max_persist ? want : (size_t)max_persist;
+            if (cur < lim) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, lim);
+            t->persist_bytes = want < (size_t)max_window ? want : (size_t)max_window;
+        }
+        cudaGetLastError();  // persistence is an optimisation; never fail creation on it
+    }
+#undef TRY_OR_BAIL
+    *out = t;
+    return MERL_OK;
+}
+
+extern "C" int merl_table_create_from_host(const double* planar_rgb, const merl_table_params_t* p, int device,
+                                           merl_table_t** out) {
+    return build_table(planar_rgb, p, device, out);
+}
+
+extern "C" int merl_table_create_from_file(const char* path, const merl_table_params_t* pin, int device,
+                                           merl_table_t** out) {
+    if (!path || !out) return fail(MERL_ERR_ARG, "NULL argument");
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(MERL_ERR_IO, "cannot open '%s'", path);
+    int32_t dims[3];
+    if (fread(dims, sizeof(int32_t), 3, f) != 3) { fclose(f); return fail(MERL_ERR_IO, "'%s': short header", path); }
+    merl_table_params_t p;
+    if (pin) p = *pin; else merl_table_params_default(&p);
+    if (p.nh == 0 && p.nd == 0 && p.np == 0) { p.nh = dims[0]; p.nd = dims[1]; p.np = dims[2]; }
+    const int64_t n = (int64_t)dims[0] * dims[1] * dims[2];
+    // the public reader's check: the product of the header must equal the expected cell count
+    if (n != (int64_t)p.nh * p.nd * p.np) {
+        fclose(f);
+        return fail(MERL_ERR_IO, "'%s': header %dx%dx%d does not match the expected %dx%dx%d cells", path, dims[0],
+                    dims[1], dims[2], p.nh, p.nd, p.np);
+    }
+    std::vector<double> raw((size_t)3 * n);
+    const size_t got = fread(raw.data(), sizeof(double), raw.size(), f);
+    fclose(f);
+    if (got != raw.size()) return fail(MERL_ERR_IO, "'%s': expected %zu doubles, read %zu", path, raw.size(), got);
+    return build_table(raw.data(), &p, device, out);
+}
+
+extern "C" int merl_table_destroy(merl_table_t* t) {
+    if (!t) return MERL_OK;
+    free_pipe(t);
+    free_table(t);
+    return MERL_OK;
+}
+
+extern "C" int merl_table_info(const merl_table_t* t, merl_table_info_t* o) {
+    if (!t || !o) return fail(MERL_ERR_ARG, "NULL argument");
+    memset(o, 0, sizeof *o);
+    o->nh = t->dev.nh; o->nd = t->dev.nd; o->np = t->dev.np; o->ni = t->dev.ni;
+    o->theta_h_sqrt = t->dev.theta_h_sqrt; o->device = t->device;
+    o->ncell = t->ncell;
+    o->table_bytes = t->ncell * (int64_t)sizeof(float4);
+    o->d_cells = t->d_cells;
+    o->d_cdf = t->d_image + t->dev.off_cdf;
+    o->d_dens = t->d_image + t->dev.off_dens;
+    o->spec_weight = t->dev.spec_weight;
+    o->smem_eval_bytes = (int32_t)eval_smem(t, true);
+    o->smem_sample_bytes = (int32_t)full_smem(t);
+    return MERL_OK;
+}
+
+extern "C" int merl_table_set_cdf(merl_table_t* t, const float* cdf_host) {
+    if (!t || !cdf_host) return fail(MERL_ERR_ARG, "NULL argument");
+    DeviceGuard g(t->device);
+    const int rc = upload_sampler(t, cdf_host, nullptr);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(nullptr));
+    return MERL_OK;
+}
+
+extern "C" int merl_table_download(const merl_table_t* t, float* cells4, float* cdf, float* dens) {
+    if (!t) return fail(MERL_ERR_ARG, "NULL argument");
+    DeviceGuard g(t->device);
+    const TableDev& d = t->dev;
+    if (cells4) CUDA_TRY(cudaMemcpy(cells4, t->d_cells, sizeof(float4) * t->ncell, cudaMemcpyDeviceToHost));
+    if (cdf) CUDA_TRY(cudaMemcpy(cdf, t->d_image + d.off_cdf, sizeof(float) * d.ni * (d.nh + 1), cudaMemcpyDeviceToHost));
+    if (dens) CUDA_TRY(cudaMemcpy(dens, t->d_image + d.off_dens, sizeof(float) * d.ni * d.nh, cudaMemcpyDeviceToHost));
+    return MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// C ABI: batched queries on device pointers
+// ------------------------------------------------------------------------------------------
+extern "C" int merl_bins(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                         const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
+                         int32_t* idx_out, merl_stream_t stream) {
+    int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > 0 && !idx_out) return fail(MERL_ERR_ARG, "idx_out is NULL");
+    DeviceGuard g(t->device);
+    const QueryIn in{wix, wiy, wiz, wox, woy, woz, active};
+    const QueryOut out{nullptr, nullptr, nullptr, nullptr, idx_out};
+    return run_query_mode<MODE_BINS>(t, in, n, out, (cudaStream_t)stream);
+}
+
+extern "C" int merl_eval(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                         const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
+                         float* r, float* g, float* b, merl_stream_t stream) {
+    int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > 0 && (!r || !g || !b)) return fail(MERL_ERR_ARG, "output pointer is NULL");
+    DeviceGuard gd(t->device);
+    const QueryIn in{wix, wiy, wiz, wox, woy, woz, active};
+    const QueryOut out{r, g, b, nullptr, nullptr};
+    return run_query_mode<MODE_EVAL>(t, in, n, out, (cudaStream_t)stream);
+}
+
+extern "C" int merl_pdf(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                        const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
+                        float* pdf, merl_stream_t stream) {
+    int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > 0 && !pdf) return fail(MERL_ERR_ARG, "output pointer is NULL");
+    DeviceGuard gd(t->device);
+    const QueryIn in{wix, wiy, wiz, wox, woy, woz, active};
+    const QueryOut out{nullptr, nullptr, nullptr, pdf, nullptr};
+    return run_query_mode<MODE_PDF>(t, in, n, out, (cudaStream_t)stream);
+}
+
+extern "C" int merl_eval_pdf(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                             const float* wox, const float* woy, const float* woz, const uint8_t* active,
+                             int64_t n, float* r, float* g, float* b, float* pdf, merl_stream_t stream) {
+    int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > 0 && (!r || !g || !b || !pdf)) return fail(MERL_ERR_ARG, "output pointer is NULL");
+    DeviceGuard gd(t->device);
+    const QueryIn in{wix, wiy, wiz, wox, woy, woz, active};
+    const QueryOut out{r, g, b, pdf, nullptr};
+    return run_query_mode<MODE_EVAL_PDF>(t, in, n, out, (cudaStream_t)stream);
+}
+
+template <int SEARCH>
+static int run_sample(const merl_table* t, SampleIn in, int64_t n, SampleOut out, cudaStream_t s) {
+    const size_t smem = full_smem(t);
+    const bool vec = aligned(in.wix, 16) && aligned(in.wiy, 16) && aligned(in.wiz, 16) && aligned(in.u1, 16) &&
+                     aligned(in.u2x, 16) && aligned(in.u2y, 16) && aligned(in.active, 4) && aligned(out.wox, 16) &&
+                     aligned(out.woy, 16) && aligned(out.woz, 16) && aligned(out.pdf, 16) && aligned(out.wr, 16) &&
+                     aligned(out.wg, 16) && aligned(out.wb, 16) && aligned(out.lobe, 16);
+    int64_t done = 0;
+    if (vec && n >= 4) {
+        const int rc = launch_persistent(t, sample_kernel<4, SEARCH>, smem, n / 4, s, t->dev, in, n / 4, out);
+        if (rc) return rc;
+        done = (n / 4) * 4;
+    }
+    if (done < n) {
+        in.wix += done; in.wiy += done; in.wiz += done; in.u1 += done; in.u2x += done; in.u2y += done;
+        if (in.active) in.active += done;
+        out.wox += done; out.woy += done; out.woz += done; out.pdf += done;
+        out.wr += done; out.wg += done; out.wb += done; out.lobe += done;
+        return launch_persistent(t, sample_kernel<1, SEARCH>, smem, n - done, s, t->dev, in, n - done, out);
+    }
+    return MERL_OK;
+}
+
+extern "C" int merl_sample(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                           const float* u1, const float* u2x, const float* u2y, const uint8_t* active, int64_t n,
+                           float* wox, float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb,
+                           uint32_t* lobe, merl_stream_t stream) {
+    int rc = check_query_args(t, wix, wiy, wiz, u1, u2x, u2y, n);
+    if (rc) return rc;
+    if (n > 0 && (!wox || !woy || !woz || !pdf || !wr || !wg || !wb || !lobe))
+        return fail(MERL_ERR_ARG, "output pointer is NULL");
+    DeviceGuard gd(t->device);
+    const SampleIn in{wix, wiy, wiz, u1, u2x, u2y, active};
+    const SampleOut out{wox, woy, woz, pdf, wr, wg, wb, lobe};
+    return g_search_mode.load() ? run_sample<1>(t, in, n, out, (cudaStream_t)stream)
+                                : run_sample<0>(t, in, n, out, (cudaStream_t)stream);
+}
+
+template <int AGG>
+static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* grad, cudaStream_t s) {
+    const size_t smem = eval_smem(t, false);
+    const QueryIn& q = in.q;
+    const bool vec = aligned(q.wix, 16) && aligned(q.wiy, 16) && aligned(q.wiz, 16) && aligned(q.wox, 16) &&
+                     aligned(q.woy, 16) && aligned(q.woz, 16) && aligned(q.active, 4) && aligned(in.gr, 16) &&
+                     aligned(in.gg, 16) && aligned(in.gb, 16);
+    int64_t done = 0;
+    if (vec && n >= 4) {
+        const int rc = launch_persistent(t, backward_kernel<4, AGG>, smem, n / 4, s, t->dev, in, n / 4, grad);
+        if (rc) return rc;
+        done = (n / 4) * 4;
+    }
+    if (done < n) {
+        in.q = offset_in(in.q, done);
+        in.gr += done; in.gg += done; in.gb += done;
+        return launch_persistent(t, backward_kernel<1, AGG>, smem, n - done, s, t->dev, in, n - done, grad);
+    }
+    return MERL_OK;
+}
+
+extern "C" int merl_backward(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                             const float* wox, const float* woy, const float* woz, const float* gr,
+                             const float* gg, const float* gb, const uint8_t* active, int64_t n,
+                             float* grad_cells4, uint32_t flags, merl_stream_t stream) {
+    int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > 0 && (!gr || !gg || !gb || !grad_cells4)) return fail(MERL_ERR_ARG, "gradient pointer is NULL");
+    if (!aligned(grad_cells4, 16)) return fail(MERL_ERR_ARG, "grad_cells4 must be 16-byte aligned");
+    DeviceGuard gd(t->device);
+    BackwardIn in{{wix, wiy, wiz, wox, woy, woz, active}, gr, gg, gb};
+    float4* grad = reinterpret_cast<float4*>(grad_cells4);
+    return (flags & MERL_BWD_WARP_AGGREGATE) ? run_backward<1>(t, in, n, grad, (cudaStream_t)stream)
+                                             : run_backward<0>(t, in, n, grad, (cudaStream_t)stream);
+}
+
+extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const float* wo4, int64_t n, float* out4,
+                                 merl_stream_t stream) {
+    if (!t || n < 0 || (n > 0 && (!wi4 || !wo4 || !out4))) return fail(MERL_ERR_ARG, "bad argument");
+    if (!aligned(wi4, 16) || !aligned(wo4, 16) || !aligned(out4, 16))
+        return fail(MERL_ERR_ARG, "AoS buffers must be 16-byte aligned");
+    DeviceGuard gd(t->device);
+    return launch_persistent(t, eval_pdf_aos_kernel, eval_smem(t, true), n, (cudaStream_t)stream, t->dev,
+                             reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(wo4), n,
+                             reinterpret_cast<float4*>(out4));
+}
+
+extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const float* u4, int64_t n, float* wo4_out,
+                               float* weight4_out, merl_stream_t stream) {
+    if (!t || n < 0 || (n > 0 && (!wi4 || !u4 || !wo4_out || !weight4_out))) return fail(MERL_ERR_ARG, "bad argument");
+    if (!aligned(wi4, 16) || !aligned(u4, 16) || !aligned(wo4_out, 16) || !aligned(weight4_out, 16))
+        return fail(MERL_ERR_ARG, "AoS buffers must be 16-byte aligned");
+    DeviceGuard gd(t->device);
+    return launch_persistent(t, sample_aos_kernel, full_smem(t), n, (cudaStream_t)stream, t->dev,
+                             reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(u4), n,
+                             reinterpret_cast<float4*>(wo4_out), reinterpret_cast<float4*>(weight4_out));
+}
+
+// ------------------------------------------------------------------------------------------
+// host-buffer entry points: chunked H2D -> kernel -> D2H over three internal streams, so the
+// two copy engines and the SMs overlap (PCIe is full duplex).  Used by scalar-variant
+// plugins and by bench.py's end-to-end leg.
+// ------------------------------------------------------------------------------------------
+struct HostPipe {
+    static constexpr int kSlots = 3;
+    static constexpr int64_t kChunk = 1 << 21;
+    cudaStream_t stream[kSlots]{};
+    float* d_in[kSlots]{};    // 6 arrays of kChunk floats
+    float* d_out[kSlots]{};   // 8 arrays of kChunk floats
+};
+
+static int get_pipe(merl_table* t, HostPipe** out) {
+    if (!t->pipe) {
+        HostPipe* p = new HostPipe();
+        for (int s = 0; s < HostPipe::kSlots; ++s) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&p->stream[s], cudaStreamNonBlocking));
+            CUDA_TRY(cudaMalloc(&p->d_in[s], sizeof(float) * 6 * HostPipe::kChunk));
+            CUDA_TRY(cudaMalloc(&p->d_out[s], sizeof(float) * 8 * HostPipe::kChunk));
+        }
+        t->pipe = p;
+    }
+    *out = static_cast<HostPipe*>(t->pipe);
+    return MERL_OK;
+}
+
+static void free_pipe(merl_table* t) {
+    if (!t || !t->pipe) return;
+    DeviceGuard g(t->device);
+    HostPipe* p = static_cast<HostPipe*>(t->pipe);
+    for (int s = 0; s < HostPipe::kSlots; ++s) {
+        if (p->stream[s]) cudaStreamDestroy(p->stream[s]);
+        cudaFree(p->d_in[s]);
+        cudaFree(p->d_out[s]);
+    }
+    delete p;
+    t->pipe = nullptr;
+}
+
+extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
+                                  const float* wox, const float* woy, const float* woz, int64_t n, float* r,
+                                  float* g, float* b, float* pdf) {
+    int rc = check_query_args(tc, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > 0 && (!r || !g || !b || !pdf)) return fail(MERL_ERR_ARG, "output pointer is NULL");
+    merl_table* t = const_cast<merl_table*>(tc);
+    DeviceGuard gd(t->device);
+    std::lock_guard<std::mutex> lk(t->host_mu);
+    HostPipe* p;
+    if ((rc = get_pipe(t, &p))) return rc;
+    const int64_t C = HostPipe::kChunk;
+    const float* src[6] = {wix, wiy, wiz, wox, woy, woz};
+    float* dst[4] = {r, g, b, pdf};
+    int slot = 0;
+    for (int64_t o = 0; o < n; o += C, slot = (slot + 1) % HostPipe::kSlots) {
+        const int64_t m = (n - o < C) ? n - o : C;
+        cudaStream_t s = p->stream[slot];
+        float* di = p->d_in[slot];
+        float* dq = p->d_out[slot];
+        for (int a = 0; a < 6; ++a)
+            CUDA_TRY(cudaMemcpyAsync(di + a * C, src[a] + o, sizeof(float) * m, cudaMemcpyHostToDevice, s));
+        const QueryIn in{di, di + C, di + 2 * C, di + 3 * C, di + 4 * C, di + 5 * C, nullptr};
+        const QueryOut out{dq, dq + C, dq + 2 * C, dq + 3 * C, nullptr};
+        if ((rc = run_query_mode<MODE_EVAL_PDF>(t, in, m, out, s))) return rc;
+        for (int a = 0; a < 4; ++a)
+            CUDA_TRY(cudaMemcpyAsync(dst[a] + o, dq + a * C, sizeof(float) * m, cudaMemcpyDeviceToHost, s));
+    }
+    for (int s = 0; s < HostPipe::kSlots; ++s) CUDA_TRY(cudaStreamSynchronize(p->stream[s]));
+    return MERL_OK;
+}
+
+extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
+                                const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
+                                float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe) {
+    int rc = check_query_args(tc, wix, wiy, wiz, u1, u2x, u2y, n);
+    if (rc) return rc;
+    if (n > 0 && (!wox || !woy || !woz || !pdf || !wr || !wg || !wb || !lobe))
+        return fail(MERL_ERR_ARG, "output pointer is NULL");
+    merl_table* t = const_cast<merl_table*>(tc);
+    DeviceGuard gd(t->device);
+    std::lock_guard<std::mutex> lk(t->host_mu);
+    HostPipe* p;
+    if ((rc = get_pipe(t, &p))) return rc;
+    const int64_t C = HostPipe::kChunk;
+    const float* src[6] = {wix, wiy, wiz, u1, u2x, u2y};
+    float* dst[8] = {wox, woy, woz, pdf, wr, wg, wb, reinterpret_cast<float*>(lobe)};
+    int slot = 0;
+    for (int64_t o = 0; o < n; o += C, slot = (slot + 1) % HostPipe::kSlots) {
+        const int64_t m = (n - o < C) ? n - o : C;
+        cudaStream_t s = p->stream[slot];
+        float* di = p->d_in[slot];
+        float* dq = p->d_out[slot];
+        for (int a = 0; a < 6; ++a)
+            CUDA_TRY(cudaMemcpyAsync(di + a * C, src[a] + o, sizeof(float) * m, cudaMemcpyHostToDevice, s));
+        const SampleIn in{di, di + C, di + 2 * C, di + 3 * C, di + 4 * C, di + 5 * C, nullptr};
+        const SampleOut out{dq, dq + C, dq + 2 * C, dq + 3 * C, dq + 4 * C, dq + 5 * C, dq + 6 * C,
+                            reinterpret_cast<uint32_t*>(dq + 7 * C)};
+        rc = g_search_mode.load() ? run_sample<1>(t, in, m, out, s) : run_sample<0>(t, in, m, out, s);
+        if (rc) return rc;
+        for (int a = 0; a < 8; ++a)
+            CUDA_TRY(cudaMemcpyAsync(dst[a] + o, dq + a * C, sizeof(float) * m, cudaMemcpyDeviceToHost, s));
+    }
+    for (int s = 0; s < HostPipe::kSlots; ++s) CUDA_TRY(cudaStreamSynchronize(p->stream[s]));
+    return MERL_OK;
+}
