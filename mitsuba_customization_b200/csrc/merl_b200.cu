@@ -308,7 +308,10 @@ __device__ __forceinline__ void cosine_hemisphere(float ux, float uy, float& x, 
     float s, c;
     sincospif(ph, &s, &c);
     x = r * c; y = r * s;
-    z = sqrtf(fmaxf(0.f, 1.f - x * x - y * y));
+    // z^2 = 1 - x^2 - y^2 = 1 - r^2, factored so that it keeps full relative accuracy at the
+    // horizon (r -> 1), where the subtraction of squares would cancel in fp32
+    const float ar = fabsf(r);
+    z = sqrtf(fmaxf(0.f, (1.f - ar) * (1.f + ar)));
 }
 
 // Largest i in [0, nh-1] with row[i] <= u: per-lane bisection over the smem-resident row.

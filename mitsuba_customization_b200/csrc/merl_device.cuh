@@ -155,7 +155,10 @@ __device__ __forceinline__ Bins compute_bins(const TableDev& t, const SmemView& 
     unsigned unc = 0;
     if (kh > 0 && kh < t.nh && !(fabsf(dh) > EPS_H * h.rho2)) unc |= 1u;
     if (kd > 0 && kd < t.nd && !(fabsf(dd) > EPS_D * h.n2)) unc |= 2u;
-    if (!(fabsf(dp) > EPS_P * (h.n2 + h.slen))) unc |= 4u;
+    // phi_d: the comparison must clear its error margin AND |(X,Y)| must be large enough that
+    // the same error cannot have moved the candidate edge itself by half a bin.
+    const float mp = EPS_P * (h.n2 + h.slen);
+    if (!(fabsf(dp) > mp) || !(fabsf(X) + Y > mp * 4.f * (float)t.np)) unc |= 4u;
     if (unc) resolve_bins_slow(t, ax, ay, az, bx, by, bz, kh, kd, kp, unc, b);
     return b;
 }

@@ -81,10 +81,20 @@ __device__ __noinline__ void resolve_bins_slow(const TableDev& t, float ax_, flo
         double X = sz * A - az * n2;
         double Y = slen * (ay * bx - ax * by);
         if (Y < 0.0) { X = -X; Y = -Y; }
-        const double2 e = t.dir_p64[kp];
-        const double dp = e.x * Y - e.y * X;
-        if (fabs(dp) > 1e-13 * (n2 + slen)) out.ip = max(min(kp - 1 + (dp >= 0.0), t.np - 1), 0);
-        else still |= 4u;
+        // Tier 1's candidate edge is unreliable here (that is one reason to be in tier 2: when
+        // |(X,Y)| is small, fp32 cancellation in X moves the direction by many bins), so the
+        // candidate is re-derived from the double (X, Y).  phi = 0 and phi = pi are the same
+        // fold edge but different bins; atan2 of the folded pair picks the right end.
+        const double m = 1e-13 * (n2 + slen);
+        if (fabs(X) + Y > m * 4.0 * t.np) {
+            kp = max(min((int)rint(atan2(Y, X) * (t.np / 3.14159265358979323846)), t.np), 0);
+            const double2 e = t.dir_p64[kp];
+            const double dp = e.x * Y - e.y * X;
+            if (fabs(dp) > m) out.ip = max(min(kp - 1 + (dp >= 0.0), t.np - 1), 0);
+            else still |= 4u;
+        } else {
+            still |= 4u;
+        }
     }
     if (still) {
         const double in[3] = {ax, ay, az}, o[3] = {bx, by, bz};

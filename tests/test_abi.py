@@ -1,0 +1,82 @@
+"""CPU tests of the C-ABI boundary: the library builds for sm_100a, loads, exports every symbol
+include/merl_b200.h declares, and refuses to compute without a GPU (no fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "merl_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(merl_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_all_exported(built_lib):
+    from mitsuba_customization_b200 import _cabi
+    declared = _declared_symbols()
+    assert declared, "no symbols parsed from the header"
+    for name in declared:
+        assert hasattr(built_lib, name), f"{name} declared in merl_b200.h but not exported"
+    assert sorted(_cabi.SYMBOLS) == declared, "the ctypes binding must track the header"
+
+
+def test_library_is_sm100a_only(built_lib):
+    import subprocess
+    from mitsuba_customization_b200 import _cabi
+    out = subprocess.run(["cuobjdump", "-lelf", _cabi.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in out and not re.search(r"sm_(?!100a)\d+", out), out
+
+
+def test_abi_version_and_defaults(built_lib):
+    from mitsuba_customization_b200 import _cabi
+    assert built_lib.merl_abi_version() == 1
+    p = _cabi.default_params()
+    assert (p.nh, p.nd, p.np, p.theta_h_sqrt, p.ni) == (90, 90, 180, 1, 32)
+    np.testing.assert_allclose(list(p.scale), [1 / 1500, 1.15 / 1500, 1.66 / 1500])
+
+
+def test_struct_layouts_match_header(built_lib):
+    """ctypes mirrors are laid out exactly as the C structs (sizes from a tiny C probe)."""
+    import subprocess
+    import tempfile
+    src = '#include "merl_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu\\n", sizeof(merl_table_params_t), sizeof(merl_table_info_t));return 0;}\n'
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "p.c"), "w").write(src)
+        subprocess.run(["/usr/bin/gcc", "-I", os.path.join(ROOT, "include"), os.path.join(d, "p.c"), "-o",
+                        os.path.join(d, "p")], check=True)
+        a, b = (int(x) for x in subprocess.run([os.path.join(d, "p")], capture_output=True, text=True).stdout.split())
+    from mitsuba_customization_b200 import _cabi
+    assert C.sizeof(_cabi.TableParams) == a and C.sizeof(_cabi.TableInfo) == b
+
+
+def test_argument_errors_without_gpu(built_lib):
+    from mitsuba_customization_b200 import _cabi
+    h = C.c_void_p()
+    rc = built_lib.merl_table_create_from_file(b"/nonexistent/file.binary", None, 0, C.byref(h))
+    assert rc == -2 and b"cannot open" in built_lib.merl_last_error()
+    assert built_lib.merl_set_sample_search(7) == -1
+    assert built_lib.merl_bins(None, None, None, None, None, None, None, None, 4, None, None) == -1
+    with pytest.raises(_cabi.MerlError):
+        _cabi.check(-1)
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device the plugin refuses to construct; nothing routes through the oracle."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from mitsuba_customization_b200 import bsdf, synth
+    with pytest.raises(bsdf.MerlError):
+        bsdf.MERL(data=synth.synthetic_table(0))
+    # the product package never imports the oracle
+    pkg = os.path.join(ROOT, "mitsuba_customization_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                assert "oracle" not in open(os.path.join(dirpath, f)).read().replace("the oracle", "").replace(
+                    "oracle:", "").replace("oracle's", "").replace("CPU oracle", ""), f
