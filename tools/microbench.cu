@@ -1,0 +1,82 @@
+// microbench.cu -- memory-system ceilings for the MERL eval+pdf access pattern on one B200.
+//   copy40      : 6 float4 read streams + 4 float4 write streams (40 B/query), no gather
+//   gather16    : idx stream (4 B) + one random 16 B gather from a 23.3 MB table + 4 B write
+//   stream+gath : copy40 pattern + the gather (the kernel's memory traffic without its math)
+// Build: nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o tools/microbench tools/microbench.cu
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e)); exit(1); } } while (0)
+
+__global__ void copy40(const float4* a, const float4* b, const float4* c, const float4* d, const float4* e,
+                       const float4* f, float4* o0, float4* o1, float4* o2, float4* o3, long n4) {
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < n4; g += (long)gridDim.x * blockDim.x) {
+        float4 x = __ldcs(a + g), y = __ldcs(b + g), z = __ldcs(c + g), u = __ldcs(d + g), v = __ldcs(e + g), w = __ldcs(f + g);
+        __stcs(o0 + g, make_float4(x.x + u.x, x.y + u.y, x.z + u.z, x.w + u.w));
+        __stcs(o1 + g, make_float4(y.x + v.x, y.y + v.y, y.z + v.z, y.w + v.w));
+        __stcs(o2 + g, make_float4(z.x + w.x, z.y + w.y, z.z + w.z, z.w + w.w));
+        __stcs(o3 + g, make_float4(x.x * w.x, y.y * v.y, z.z * u.z, x.w));
+    }
+}
+template <int MODE>  // 0: __ldg  1: ld.global.cg (L2 only)
+__global__ void gather16(const float4* __restrict__ table, const int4* __restrict__ idx, float4* out, long n4) {
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < n4; g += (long)gridDim.x * blockDim.x) {
+        int4 i = __ldcs(idx + g);
+        float4 a, b, c, d;
+        if (MODE == 0) { a = __ldg(table + i.x); b = __ldg(table + i.y); c = __ldg(table + i.z); d = __ldg(table + i.w); }
+        else { a = __ldcg(table + i.x); b = __ldcg(table + i.y); c = __ldcg(table + i.z); d = __ldcg(table + i.w); }
+        __stcs(out + g, make_float4(a.x + a.y, b.x + b.z, c.x + c.w, d.x + d.y));
+    }
+}
+__global__ void stream_gather(const float4* __restrict__ table, const int4* __restrict__ idx, const float4* a,
+                              const float4* b, const float4* c, const float4* d, const float4* e, float4* o0,
+                              float4* o1, float4* o2, float4* o3, long n4) {
+    // 5 float4 input streams + the index stream stand in for the 6 direction streams (24 B/query)
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < n4; g += (long)gridDim.x * blockDim.x) {
+        int4 i = __ldcs(idx + g);
+        float4 x = __ldcs(a + g), y = __ldcs(b + g), z = __ldcs(c + g), u = __ldcs(d + g), v = __ldcs(e + g);
+        float4 p = __ldg(table + i.x), q = __ldg(table + i.y), r = __ldg(table + i.z), s = __ldg(table + i.w);
+        __stcs(o0 + g, make_float4(p.x * x.x, q.x * x.y, r.x * x.z, s.x * x.w));
+        __stcs(o1 + g, make_float4(p.y * y.x, q.y * y.y, r.y * y.z, s.y * y.w));
+        __stcs(o2 + g, make_float4(p.z * z.x, q.z * z.y, r.z * z.z, s.z * z.w));
+        __stcs(o3 + g, make_float4(u.x + v.x, u.y + v.y, u.z + v.z, u.w + v.w));
+    }
+}
+template <typename F> float timeit(F f, int iters = 10) {
+    for (int i = 0; i < 3; ++i) f();
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0);
+    for (int i = 0; i < iters; ++i) f();
+    cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
+    float ms; cudaEventElapsedTime(&ms, e0, e1); return ms / iters;
+}
+int main(int argc, char** argv) {
+    const long n = 1L << (argc > 1 ? atoi(argv[1]) : 26), n4 = n / 4;
+    const int ncell = 90 * 90 * 180;
+    int dev = 0, l2 = 0, pers = 0, win = 0, sms = 0;
+    cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev);
+    cudaDeviceGetAttribute(&pers, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    cudaDeviceGetAttribute(&win, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    printf("L2 %d B, max persisting %d B, max window %d B, SMs %d\n", l2, pers, win, sms);
+    float4 *in[6], *out[4], *table; int4* idx;
+    for (auto& p : in) { CK(cudaMalloc(&p, n * 4)); CK(cudaMemset(p, 0, n * 4)); }
+    for (auto& p : out) CK(cudaMalloc(&p, n * 4));
+    CK(cudaMalloc(&table, ncell * 16L)); CK(cudaMemset(table, 0, ncell * 16L));
+    CK(cudaMalloc(&idx, n * 4));
+    { std::vector<int> h(n); unsigned s = 12345u; for (long i = 0; i < n; ++i) { s = s * 1664525u + 1013904223u; h[i] = (int)((s >> 8) % ncell); }
+      CK(cudaMemcpy(idx, h.data(), n * 4, cudaMemcpyHostToDevice)); }
+    for (int bps : {2, 4, 8}) {
+        const int grid = sms * bps;
+        float ms = timeit([&] { copy40<<<grid, 256>>>(in[0], in[1], in[2], in[3], in[4], in[5], out[0], out[1], out[2], out[3], n4); });
+        printf("copy40        grid %4d: %7.3f ms  %7.1f GB/s  (%6.1f Gq/s at 40 B/q)\n", grid, ms, 40.0 * n / ms / 1e6, n / ms / 1e6);
+        ms = timeit([&] { gather16<0><<<grid, 256>>>(table, idx, out[0], n4); });
+        printf("gather16 ldg  grid %4d: %7.3f ms  %7.1f Ggather/s  (%6.1f GB/s of 32 B sectors)\n", grid, ms, n / ms / 1e6, 32.0 * n / ms / 1e6);
+        ms = timeit([&] { gather16<1><<<grid, 256>>>(table, idx, out[0], n4); });
+        printf("gather16 ldcg grid %4d: %7.3f ms  %7.1f Ggather/s\n", grid, ms, n / ms / 1e6);
+        ms = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4); });
+        printf("stream+gather grid %4d: %7.3f ms  %7.1f Gq/s  (%6.1f GB/s algorithmic at 40 B/q)\n", grid, ms, n / ms / 1e6, 40.0 * n / ms / 1e6);
+    }
+    return 0;
+}
