@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libmerl_b200.so")
+LIB_PATH = os.environ.get("MERL_B200_LIB") or os.path.join(_PKG, "libmerl_b200.so")  # env: tuning builds only
 
 # every symbol include/merl_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [

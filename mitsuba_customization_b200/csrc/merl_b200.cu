@@ -22,6 +22,7 @@
 #include "merl_device.cuh"
 #include "merl_slow.cuh"
 
+
 using namespace merl;
 
 // ------------------------------------------------------------------------------------------
@@ -200,6 +201,10 @@ template <int VEC> __device__ __forceinline__ Pack<VEC> load_stream(const float*
 template <> __device__ __forceinline__ Pack<1> load_stream<1>(const float* p, int64_t g) {
     Pack<1> r; r.v[0] = __ldcs(p + g); return r;
 }
+template <> __device__ __forceinline__ Pack<2> load_stream<2>(const float* p, int64_t g) {
+    const float2 f = __ldcs(reinterpret_cast<const float2*>(p) + g);
+    Pack<2> r; r.v[0] = f.x; r.v[1] = f.y; return r;
+}
 template <> __device__ __forceinline__ Pack<4> load_stream<4>(const float* p, int64_t g) {
     const float4 f = __ldcs(reinterpret_cast<const float4*>(p) + g);
     Pack<4> r; r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w; return r;
@@ -208,12 +213,20 @@ template <int VEC> __device__ __forceinline__ void store_stream(float* p, int64_
 template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g, const Pack<1>& a) {
     __stcs(p + g, a.v[0]);
 }
+template <> __device__ __forceinline__ void store_stream<2>(float* p, int64_t g, const Pack<2>& a) {
+    __stcs(reinterpret_cast<float2*>(p) + g, make_float2(a.v[0], a.v[1]));
+}
 template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g, const Pack<4>& a) {
     __stcs(reinterpret_cast<float4*>(p) + g, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
 }
 template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
 template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
     return p ? (p[g] != 0) : 1u;
+}
+template <> __device__ __forceinline__ unsigned load_active<2>(const uint8_t* p, int64_t g) {
+    if (!p) return 0x3u;
+    const uint16_t w = __ldcs(reinterpret_cast<const uint16_t*>(p) + g);
+    return ((w & 0xFFu) != 0) | ((w >> 8) != 0) << 1;
 }
 template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p, int64_t g) {
     if (!p) return 0xFu;
@@ -230,10 +243,11 @@ struct QueryIn {
 // pdf of the two-lobe sampler given the bins (row A5; oracle: eval_pdf_one).
 __device__ __forceinline__ float pdf_from_bins(const TableDev& t, const SmemView& v, float az, float bz,
                                                const HalfDiff& h, int ih) {
-    const int j = min((int)(az * (float)t.ni), t.ni - 1);
-    float p = (1.f - t.spec_weight) * bz * 0.318309886f;
-    if (h.A > 0.f) p = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
-    return p;
+    // branch-free: the density is read for every lane (clamped slice index) and selected
+    const int j = max(min((int)(az * (float)t.ni), t.ni - 1), 0);
+    const float p = (1.f - t.spec_weight) * bz * 0.318309886f;
+    const float ps = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
+    return h.A > 0.f ? ps : p;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -246,52 +260,150 @@ struct QueryOut {
     int32_t* idx;
 };
 
+// ------------------------------------------------------------------------------------------
+// Deferred exactness.  The streaming loop runs tier 1 only (branch-free, no fp64, ~40 fewer
+// registers).  A query whose tier-1 decision was inside its error margin (~1.3e-3 of uniform
+// queries) is appended to the warp's private queue in shared memory and re-done exactly
+// (tiers 2-3, merl_slow.cuh) when the queue fills or the warp runs out of work.  The redo
+// overwrites that query's outputs, so results are those of the all-tiers computation for every
+// input, including adversarial batches in which every query is uncertain (the warp then
+// flushes every iteration: slow, still exact).  No scratch memory, no second launch.
+// ------------------------------------------------------------------------------------------
+constexpr int kWarpsPerCta = 8;
+constexpr int kQueueCap = 256;                      // entries per warp (8 B each)
+constexpr int kQueueBytes = kWarpsPerCta * (kQueueCap * 8 + 8);
+
+struct WarpQueue {
+    int64_t* items;   // [kQueueCap] absolute query indices
+    int* count;
+};
+__device__ __forceinline__ WarpQueue warp_queue(char* base, int warp) {
+    WarpQueue q;
+    q.items = reinterpret_cast<int64_t*>(base) + warp * kQueueCap;
+    q.count = reinterpret_cast<int*>(base + kWarpsPerCta * kQueueCap * 8) + warp * 2;
+    return q;
+}
+__device__ __forceinline__ void queue_push(const WarpQueue& q, int64_t query) {
+    q.items[atomicAdd(q.count, 1)] = query;
+}
+
+// One group of VEC consecutive queries, tier 1 only: bins -> gather -> outputs.  `uncmask` gets
+// bit q set when query q of the group must be re-done.
 template <int MODE, int VEC>
-__global__ void __launch_bounds__(256) query_kernel(const TableDev t, const QueryIn in, const int64_t ngroups,
-                                                    const QueryOut out) {
+__device__ __forceinline__ void process_group(const TableDev& t, const SmemView& v, const Pack<VEC>& ax,
+                                              const Pack<VEC>& ay, const Pack<VEC>& az, const Pack<VEC>& bx,
+                                              const Pack<VEC>& by, const Pack<VEC>& bz, const unsigned act,
+                                              const int64_t g, const QueryOut& out, unsigned& uncmask) {
     constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
     constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
-    extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
-    stage_image(t, smem, kPdf ? t.image_eval_floats : t.off_dens);
-    const SmemView v = make_view(t, smem);
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < ngroups; g += stride) {
-        const Pack<VEC> ax = load_stream<VEC>(in.wix, g), ay = load_stream<VEC>(in.wiy, g),
-                        az = load_stream<VEC>(in.wiz, g), bx = load_stream<VEC>(in.wox, g),
-                        by = load_stream<VEC>(in.woy, g), bz = load_stream<VEC>(in.woz, g);
-        const unsigned act = load_active<VEC>(in.active, g);
-        int idx[VEC];
-        Pack<VEC> pdf;
-        bool valid[VEC];
+    int idx[VEC];
+    Pack<VEC> pdf;
+    bool valid[VEC];
+    uncmask = 0;
+#pragma unroll
+    for (int q = 0; q < VEC; ++q) {
+        valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
+        const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
+        unsigned unc;
+        int kc[3];
+        const Bins b = compute_bins_fast(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h, unc, kc);
+        uncmask |= (unsigned)((unc != 0u) & valid[q]) << q;
+        idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
+        if (kPdf) {
+            const float pq = pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih);
+            pdf.v[q] = valid[q] ? pq : 0.f;
+        }
+    }
+    if (kEval) {
+        float4 cell[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
+        Pack<VEC> r, gg, bb;
 #pragma unroll
         for (int q = 0; q < VEC; ++q) {
-            valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
-            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
-            const Bins b = compute_bins(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h);
-            idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
-            if (kPdf) pdf.v[q] = valid[q] ? pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih) : 0.f;
+            const float c = valid[q] ? bz.v[q] : 0.f;
+            r.v[q] = cell[q].x * c; gg.v[q] = cell[q].y * c; bb.v[q] = cell[q].z * c;
         }
-        if (kEval) {
-            float4 cell[VEC];
-#pragma unroll
-            for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
-            Pack<VEC> r, gg, bb;
-#pragma unroll
-            for (int q = 0; q < VEC; ++q) {
-                const float c = valid[q] ? bz.v[q] : 0.f;
-                r.v[q] = cell[q].x * c; gg.v[q] = cell[q].y * c; bb.v[q] = cell[q].z * c;
-            }
-            store_stream<VEC>(out.r, g, r);
-            store_stream<VEC>(out.g, g, gg);
-            store_stream<VEC>(out.b, g, bb);
-        }
-        if (kPdf) store_stream<VEC>(out.pdf, g, pdf);
-        if (MODE == MODE_BINS) {
+        store_stream<VEC>(out.r, g, r);
+        store_stream<VEC>(out.g, g, gg);
+        store_stream<VEC>(out.b, g, bb);
+    }
+    if (kPdf) store_stream<VEC>(out.pdf, g, pdf);
+    if (MODE == MODE_BINS) {
+        if (VEC == 4) {
+            reinterpret_cast<int4*>(out.idx)[g] =
+                make_int4(valid[0] ? idx[0] : -1, valid[VEC > 1 ? 1 : 0] ? idx[VEC > 1 ? 1 : 0] : -1,
+                          valid[VEC > 2 ? 2 : 0] ? idx[VEC > 2 ? 2 : 0] : -1,
+                          valid[VEC > 3 ? 3 : 0] ? idx[VEC > 3 ? 3 : 0] : -1);
+        } else {
 #pragma unroll
             for (int q = 0; q < VEC; ++q) out.idx[g * VEC + q] = valid[q] ? idx[q] : -1;
         }
     }
+}
+
+// Exact redo of one query (all tiers) with scalar loads and stores.  Only queries that were
+// valid and uncertain get here.
+template <int MODE>
+__device__ __forceinline__ void redo_query(const TableDev& t, const SmemView& v, const QueryIn& in, const int64_t i,
+                                        const QueryOut& out) {
+    constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
+    constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
+    const float ax = in.wix[i], ay = in.wiy[i], az = in.wiz[i], bx = in.wox[i], by = in.woy[i], bz = in.woz[i];
+    const HalfDiff h = half_diff_setup(ax, ay, az, bx, by, bz);
+    const Bins b = compute_bins(t, v, ax, ay, az, bx, by, bz, h);
+    const int idx = (b.ih * t.nd + b.id) * t.np + b.ip;
+    if (kEval) {
+        const float4 cell = __ldg(&t.cells[idx]);
+        out.r[i] = cell.x * bz; out.g[i] = cell.y * bz; out.b[i] = cell.z * bz;
+    }
+    if (kPdf) out.pdf[i] = pdf_from_bins(t, v, az, bz, h, b.ih);
+    if (MODE == MODE_BINS) out.idx[i] = idx;
+}
+
+template <int MODE>
+__device__ __forceinline__ void flush_queue(const TableDev& t, const SmemView& v, const QueryIn& in,
+                                            const QueryOut& out, const WarpQueue& wq, const int lane) {
+    __syncwarp();   // orders the streaming stores of this warp before the redo stores
+    const int n = *reinterpret_cast<volatile int*>(wq.count);
+    for (int e = lane; e < n; e += 32) redo_query<MODE>(t, v, in, wq.items[e], out);
+    __syncwarp();
+    if (lane == 0) *reinterpret_cast<volatile int*>(wq.count) = 0;
+    __syncwarp();
+}
+
+template <int MODE, int VEC, int MINB>
+__global__ void __launch_bounds__(256, MINB) query_kernel(const TableDev t, const QueryIn in, const int64_t ngroups,
+                                                          const QueryOut out, const int image_bytes) {
+    constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const WarpQueue wq = warp_queue(reinterpret_cast<char*>(smem4) + image_bytes, warp);
+    if (lane == 0) *wq.count = 0;
+    stage_image(t, smem, kPdf ? t.image_eval_floats : t.off_dens);   // ends with __syncthreads()
+    const SmemView v = make_view(t, smem);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // warp-uniform trip count: the queue flush uses warp-level synchronisation
+    for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
+        const int64_t g = g0 + lane;
+        if (g < ngroups) {
+            const Pack<VEC> ax = load_stream<VEC>(in.wix, g), ay = load_stream<VEC>(in.wiy, g),
+                            az = load_stream<VEC>(in.wiz, g), bx = load_stream<VEC>(in.wox, g),
+                            by = load_stream<VEC>(in.woy, g), bz = load_stream<VEC>(in.woz, g);
+            const unsigned act = load_active<VEC>(in.active, g);
+            unsigned uncmask;
+            process_group<MODE, VEC>(t, v, ax, ay, az, bx, by, bz, act, g, out, uncmask);
+            if (uncmask) {
+#pragma unroll
+                for (int q = 0; q < VEC; ++q)
+                    if ((uncmask >> q) & 1u) queue_push(wq, g * VEC + q);
+            }
+        }
+        __syncwarp();
+        if (*reinterpret_cast<volatile int*>(wq.count) > kQueueCap - 32 * VEC) flush_queue<MODE>(t, v, in, out, wq, lane);
+    }
+    flush_queue<MODE>(t, v, in, out, wq, lane);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -588,7 +700,8 @@ __global__ void __launch_bounds__(256) sample_aos_kernel(const TableDev t, const
 // host: launch plumbing
 // ------------------------------------------------------------------------------------------
 static constexpr int kThreads = 256;
-static constexpr size_t kMaxSmemBytes = 100 * 1024;
+static constexpr size_t kMaxSmemBytes = 100 * 1024;   // per-table image (edges, densities, CDF rows)
+static constexpr size_t kMaxDynSmem = 227 * 1024;     // sm_100a opt-in limit per CTA
 
 template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
     // cached per (kernel instantiation, smem size)
@@ -598,7 +711,7 @@ template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
     const std::pair<const void*, size_t> key((const void*)kernel, smem);
     for (auto& e : cache)
         if (e.first == key) return e.second;
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmemBytes);
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
     int nb = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kThreads, smem) != cudaSuccess || nb < 1) nb = 1;
     cache.push_back({key, nb});
@@ -652,21 +765,26 @@ static QueryOut offset_out(QueryOut q, int64_t o) {
     return q;
 }
 
+// Shared-memory layout of the streaming kernels: [table image, 128-byte rounded][warp queues].
+static inline int image_bytes(size_t image) { return (int)((image + 127) & ~(size_t)127); }
+
 template <int MODE>
 static int run_query_mode(const merl_table* t, const QueryIn& in, int64_t n, const QueryOut& out, cudaStream_t s) {
-    const size_t smem = eval_smem(t, MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
+    const int img = image_bytes(eval_smem(t, MODE == MODE_PDF || MODE == MODE_EVAL_PDF));
+    const size_t smem = (size_t)img + kQueueBytes;
     const bool vec = aligned(in.wix, 16) && aligned(in.wiy, 16) && aligned(in.wiz, 16) && aligned(in.wox, 16) &&
                      aligned(in.woy, 16) && aligned(in.woz, 16) && aligned(in.active, 4) && aligned(out.r, 16) &&
                      aligned(out.g, 16) && aligned(out.b, 16) && aligned(out.pdf, 16) && aligned(out.idx, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_persistent(t, query_kernel<MODE, 4>, smem, n / 4, s, t->dev, in, n / 4, out);
+        const int64_t ng = n / 4;
+        const int rc = launch_persistent(t, query_kernel<MODE, 4, 3>, smem, ng, s, t->dev, in, ng, out, img);
         if (rc) return rc;
-        done = (n / 4) * 4;
+        done = ng * 4;
     }
     if (done < n)
-        return launch_persistent(t, query_kernel<MODE, 1>, smem, n - done, s, t->dev, offset_in(in, done), n - done,
-                                 offset_out(out, done));
+        return launch_persistent(t, query_kernel<MODE, 1, 4>, smem, n - done, s, t->dev, offset_in(in, done), n - done,
+                                 offset_out(out, done), img);
     return MERL_OK;
 }
 

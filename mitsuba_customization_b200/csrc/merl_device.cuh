@@ -128,9 +128,12 @@ __device__ __noinline__ void resolve_bins_slow(const TableDev& t, float ax_, flo
                                                float bx_, float by_, float bz_, int kh, int kd, int kp,
                                                unsigned unc, Bins& out);
 
-// Tier 1.  Returns the bins; falls through to resolve_bins_slow for uncertain lanes.
-__device__ __forceinline__ Bins compute_bins(const TableDev& t, const SmemView& v, float ax, float ay,
-                                             float az, float bx, float by, float bz, const HalfDiff& h) {
+// Tier 1.  Returns the tier-1 bins and, in `unc`, which coordinates (bit 0/1/2 = theta_h /
+// theta_d / phi_d) were decided inside their error margin and therefore need tiers 2-3.
+// kc[] receives the candidate edges the slow tiers start from.
+__device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemView& v, float ax, float ay,
+                                                  float az, float bx, float by, float bz, const HalfDiff& h,
+                                                  unsigned& unc, int kc[3]) {
     constexpr float EPS_H = 2e-6f, EPS_D = 2e-6f, EPS_P = 1.5e-6f;  // error budgets: DESIGN.md §3
     // candidates
     const float th_h = fast_atan2_pos(sqrt_approx(h.rho2), h.sz);
@@ -152,14 +155,27 @@ __device__ __forceinline__ Bins compute_bins(const TableDev& t, const SmemView& 
     b.ih = max(min(kh - 1 + (dh >= 0.f), t.nh - 1), 0);  // max(): NaN inputs must not index out of range
     b.id = max(min(kd - 1 + (dd >= 0.f), t.nd - 1), 0);
     b.ip = max(min(kp - 1 + (dp >= 0.f), t.np - 1), 0);
-    unsigned unc = 0;
-    if (kh > 0 && kh < t.nh && !(fabsf(dh) > EPS_H * h.rho2)) unc |= 1u;
-    if (kd > 0 && kd < t.nd && !(fabsf(dd) > EPS_D * h.n2)) unc |= 2u;
+    // (bitwise, not short-circuit: the streaming loop must stay branch-free so that the four
+    // queries a thread holds interleave)
+    const float mp = EPS_P * (h.n2 + h.slen);
+    const bool uh = (kh > 0) & (kh < t.nh) & !(fabsf(dh) > EPS_H * h.rho2);
+    const bool ud = (kd > 0) & (kd < t.nd) & !(fabsf(dd) > EPS_D * h.n2);
     // phi_d: the comparison must clear its error margin AND |(X,Y)| must be large enough that
     // the same error cannot have moved the candidate edge itself by half a bin.
-    const float mp = EPS_P * (h.n2 + h.slen);
-    if (!(fabsf(dp) > mp) || !(fabsf(X) + Y > mp * 4.f * (float)t.np)) unc |= 4u;
-    if (unc) resolve_bins_slow(t, ax, ay, az, bx, by, bz, kh, kd, kp, unc, b);
+    const bool up = !(fabsf(dp) > mp) | !(fabsf(X) + Y > mp * 4.f * (float)t.np);
+    unc = (unsigned)uh | ((unsigned)ud << 1) | ((unsigned)up << 2);
+    kc[0] = kh; kc[1] = kd; kc[2] = kp;
+    return b;
+}
+
+// All three tiers inline: the exact bins of one query.  Used by the redo path of the streaming
+// kernels (uncertain queries only), by the table-build kernels and by the AoS kernels.
+__device__ __forceinline__ Bins compute_bins(const TableDev& t, const SmemView& v, float ax, float ay,
+                                             float az, float bx, float by, float bz, const HalfDiff& h) {
+    unsigned unc;
+    int kc[3];
+    Bins b = compute_bins_fast(t, v, ax, ay, az, bx, by, bz, h, unc, kc);
+    if (unc) resolve_bins_slow(t, ax, ay, az, bx, by, bz, kc[0], kc[1], kc[2], unc, b);
     return b;
 }
 
