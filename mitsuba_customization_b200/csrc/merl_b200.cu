@@ -1,11 +1,8 @@
 // merl_b200.cu -- libmerl_b200: C ABI (include/merl_b200.h) + sm_100a kernels.
 //
-// Kernels:  repack_kernel, cdf_build_kernel, dens_kernel (table build, one-off)
-//                          query_kernel<MODE,VEC>  (bins / eval / pdf / eval_pdf)
-//                          sample_kernel<VEC,SEARCH>, backward_kernel<VEC,AGG>
-// All query kernels are persistent grid-stride kernels sized to the SM count, stage the
-// per-table edge/density image in shared memory once per CTA, stream queries with 16-byte
-// SoA loads (evict-first) and gather one float4 per query from the L2-pinned table.
+// Kernels:  repack_kernel, cdf_build_kernel, dens_kernel (table build, one-off; here)
+//                          stream_kernel<Op> with Op = QueryOp / SampleOp / BackwardOp /
+//                          EvalPdfAosOp / SampleAosOp (merl_kernels.cuh)
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdarg.h>
@@ -19,8 +16,7 @@
 #include <vector>
 
 #include "../../include/merl_b200.h"
-#include "merl_device.cuh"
-#include "merl_slow.cuh"
+#include "merl_kernels.cuh"
 
 
 using namespace merl;
@@ -193,510 +189,6 @@ __global__ void dens_kernel(const float* __restrict__ cdf, const double* __restr
 }
 
 // ------------------------------------------------------------------------------------------
-// streamed SoA access: VEC consecutive queries per thread, 16-byte evict-first transactions
-// ------------------------------------------------------------------------------------------
-template <int VEC> struct Pack { float v[VEC]; };
-
-template <int VEC> __device__ __forceinline__ Pack<VEC> load_stream(const float* p, int64_t g);
-template <> __device__ __forceinline__ Pack<1> load_stream<1>(const float* p, int64_t g) {
-    Pack<1> r; r.v[0] = __ldcs(p + g); return r;
-}
-template <> __device__ __forceinline__ Pack<2> load_stream<2>(const float* p, int64_t g) {
-    const float2 f = __ldcs(reinterpret_cast<const float2*>(p) + g);
-    Pack<2> r; r.v[0] = f.x; r.v[1] = f.y; return r;
-}
-template <> __device__ __forceinline__ Pack<4> load_stream<4>(const float* p, int64_t g) {
-    const float4 f = __ldcs(reinterpret_cast<const float4*>(p) + g);
-    Pack<4> r; r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w; return r;
-}
-template <int VEC> __device__ __forceinline__ void store_stream(float* p, int64_t g, const Pack<VEC>& a);
-template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g, const Pack<1>& a) {
-    __stcs(p + g, a.v[0]);
-}
-template <> __device__ __forceinline__ void store_stream<2>(float* p, int64_t g, const Pack<2>& a) {
-    __stcs(reinterpret_cast<float2*>(p) + g, make_float2(a.v[0], a.v[1]));
-}
-template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g, const Pack<4>& a) {
-    __stcs(reinterpret_cast<float4*>(p) + g, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
-}
-template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
-template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
-    return p ? (p[g] != 0) : 1u;
-}
-template <> __device__ __forceinline__ unsigned load_active<2>(const uint8_t* p, int64_t g) {
-    if (!p) return 0x3u;
-    const uint16_t w = __ldcs(reinterpret_cast<const uint16_t*>(p) + g);
-    return ((w & 0xFFu) != 0) | ((w >> 8) != 0) << 1;
-}
-template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p, int64_t g) {
-    if (!p) return 0xFu;
-    const uint32_t w = __ldcs(reinterpret_cast<const uint32_t*>(p) + g);
-    return ((w & 0xFFu) != 0) | (((w >> 8) & 0xFFu) != 0) << 1 | (((w >> 16) & 0xFFu) != 0) << 2 |
-           ((w >> 24) != 0) << 3;
-}
-
-struct QueryIn {
-    const float *wix, *wiy, *wiz, *wox, *woy, *woz;
-    const uint8_t* active;
-};
-
-// pdf of the two-lobe sampler given the bins (row A5; oracle: eval_pdf_one).
-__device__ __forceinline__ float pdf_from_bins(const TableDev& t, const SmemView& v, float az, float bz,
-                                               const HalfDiff& h, int ih) {
-    // branch-free: the density is read for every lane (clamped slice index) and selected
-    const int j = max(min((int)(az * (float)t.ni), t.ni - 1), 0);
-    const float p = (1.f - t.spec_weight) * bz * 0.318309886f;
-    const float ps = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
-    return h.A > 0.f ? ps : p;
-}
-
-// ------------------------------------------------------------------------------------------
-// bins / eval / pdf / eval_pdf   (rows A1-A5)
-// ------------------------------------------------------------------------------------------
-enum QueryMode { MODE_BINS = 0, MODE_EVAL = 1, MODE_PDF = 2, MODE_EVAL_PDF = 3 };
-
-struct QueryOut {
-    float *r, *g, *b, *pdf;
-    int32_t* idx;
-};
-
-// ------------------------------------------------------------------------------------------
-// Deferred exactness.  The streaming loop runs tier 1 only (branch-free, no fp64, ~40 fewer
-// registers).  A query whose tier-1 decision was inside its error margin (~1.3e-3 of uniform
-// queries) is appended to the warp's private queue in shared memory and re-done exactly
-// (tiers 2-3, merl_slow.cuh) when the queue fills or the warp runs out of work.  The redo
-// overwrites that query's outputs, so results are those of the all-tiers computation for every
-// input, including adversarial batches in which every query is uncertain (the warp then
-// flushes every iteration: slow, still exact).  No scratch memory, no second launch.
-// ------------------------------------------------------------------------------------------
-constexpr int kWarpsPerCta = 8;
-constexpr int kQueueCap = 256;                      // entries per warp (8 B each)
-constexpr int kQueueBytes = kWarpsPerCta * (kQueueCap * 8 + 8);
-
-struct WarpQueue {
-    int64_t* items;   // [kQueueCap] absolute query indices
-    int* count;
-};
-__device__ __forceinline__ WarpQueue warp_queue(char* base, int warp) {
-    WarpQueue q;
-    q.items = reinterpret_cast<int64_t*>(base) + warp * kQueueCap;
-    q.count = reinterpret_cast<int*>(base + kWarpsPerCta * kQueueCap * 8) + warp * 2;
-    return q;
-}
-__device__ __forceinline__ void queue_push(const WarpQueue& q, int64_t query) {
-    q.items[atomicAdd(q.count, 1)] = query;
-}
-
-// One group of VEC consecutive queries, tier 1 only: bins -> gather -> outputs.  `uncmask` gets
-// bit q set when query q of the group must be re-done.
-template <int MODE, int VEC>
-__device__ __forceinline__ void process_group(const TableDev& t, const SmemView& v, const Pack<VEC>& ax,
-                                              const Pack<VEC>& ay, const Pack<VEC>& az, const Pack<VEC>& bx,
-                                              const Pack<VEC>& by, const Pack<VEC>& bz, const unsigned act,
-                                              const int64_t g, const QueryOut& out, unsigned& uncmask) {
-    constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
-    constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
-    int idx[VEC];
-    Pack<VEC> pdf;
-    bool valid[VEC];
-    uncmask = 0;
-#pragma unroll
-    for (int q = 0; q < VEC; ++q) {
-        valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
-        const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
-        unsigned unc;
-        int kc[3];
-        const Bins b = compute_bins_fast(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h, unc, kc);
-        uncmask |= (unsigned)((unc != 0u) & valid[q]) << q;
-        idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
-        if (kPdf) {
-            const float pq = pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih);
-            pdf.v[q] = valid[q] ? pq : 0.f;
-        }
-    }
-    if (kEval) {
-        float4 cell[VEC];
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
-        Pack<VEC> r, gg, bb;
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) {
-            const float c = valid[q] ? bz.v[q] : 0.f;
-            r.v[q] = cell[q].x * c; gg.v[q] = cell[q].y * c; bb.v[q] = cell[q].z * c;
-        }
-        store_stream<VEC>(out.r, g, r);
-        store_stream<VEC>(out.g, g, gg);
-        store_stream<VEC>(out.b, g, bb);
-    }
-    if (kPdf) store_stream<VEC>(out.pdf, g, pdf);
-    if (MODE == MODE_BINS) {
-        if (VEC == 4) {
-            reinterpret_cast<int4*>(out.idx)[g] =
-                make_int4(valid[0] ? idx[0] : -1, valid[VEC > 1 ? 1 : 0] ? idx[VEC > 1 ? 1 : 0] : -1,
-                          valid[VEC > 2 ? 2 : 0] ? idx[VEC > 2 ? 2 : 0] : -1,
-                          valid[VEC > 3 ? 3 : 0] ? idx[VEC > 3 ? 3 : 0] : -1);
-        } else {
-#pragma unroll
-            for (int q = 0; q < VEC; ++q) out.idx[g * VEC + q] = valid[q] ? idx[q] : -1;
-        }
-    }
-}
-
-// Exact redo of one query (all tiers) with scalar loads and stores.  Only queries that were
-// valid and uncertain get here.
-template <int MODE>
-__device__ __forceinline__ void redo_query(const TableDev& t, const SmemView& v, const QueryIn& in, const int64_t i,
-                                        const QueryOut& out) {
-    constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
-    constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
-    const float ax = in.wix[i], ay = in.wiy[i], az = in.wiz[i], bx = in.wox[i], by = in.woy[i], bz = in.woz[i];
-    const HalfDiff h = half_diff_setup(ax, ay, az, bx, by, bz);
-    const Bins b = compute_bins(t, v, ax, ay, az, bx, by, bz, h);
-    const int idx = (b.ih * t.nd + b.id) * t.np + b.ip;
-    if (kEval) {
-        const float4 cell = __ldg(&t.cells[idx]);
-        out.r[i] = cell.x * bz; out.g[i] = cell.y * bz; out.b[i] = cell.z * bz;
-    }
-    if (kPdf) out.pdf[i] = pdf_from_bins(t, v, az, bz, h, b.ih);
-    if (MODE == MODE_BINS) out.idx[i] = idx;
-}
-
-template <int MODE>
-__device__ __forceinline__ void flush_queue(const TableDev& t, const SmemView& v, const QueryIn& in,
-                                            const QueryOut& out, const WarpQueue& wq, const int lane) {
-    __syncwarp();   // orders the streaming stores of this warp before the redo stores
-    const int n = *reinterpret_cast<volatile int*>(wq.count);
-    for (int e = lane; e < n; e += 32) redo_query<MODE>(t, v, in, wq.items[e], out);
-    __syncwarp();
-    if (lane == 0) *reinterpret_cast<volatile int*>(wq.count) = 0;
-    __syncwarp();
-}
-
-template <int MODE, int VEC, int MINB>
-__global__ void __launch_bounds__(256, MINB) query_kernel(const TableDev t, const QueryIn in, const int64_t ngroups,
-                                                          const QueryOut out, const int image_bytes) {
-    constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
-    extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const WarpQueue wq = warp_queue(reinterpret_cast<char*>(smem4) + image_bytes, warp);
-    if (lane == 0) *wq.count = 0;
-    stage_image(t, smem, kPdf ? t.image_eval_floats : t.off_dens);   // ends with __syncthreads()
-    const SmemView v = make_view(t, smem);
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    // warp-uniform trip count: the queue flush uses warp-level synchronisation
-    for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
-        const int64_t g = g0 + lane;
-        if (g < ngroups) {
-            const Pack<VEC> ax = load_stream<VEC>(in.wix, g), ay = load_stream<VEC>(in.wiy, g),
-                            az = load_stream<VEC>(in.wiz, g), bx = load_stream<VEC>(in.wox, g),
-                            by = load_stream<VEC>(in.woy, g), bz = load_stream<VEC>(in.woz, g);
-            const unsigned act = load_active<VEC>(in.active, g);
-            unsigned uncmask;
-            process_group<MODE, VEC>(t, v, ax, ay, az, bx, by, bz, act, g, out, uncmask);
-            if (uncmask) {
-#pragma unroll
-                for (int q = 0; q < VEC; ++q)
-                    if ((uncmask >> q) & 1u) queue_push(wq, g * VEC + q);
-            }
-        }
-        __syncwarp();
-        if (*reinterpret_cast<volatile int*>(wq.count) > kQueueCap - 32 * VEC) flush_queue<MODE>(t, v, in, out, wq, lane);
-    }
-    flush_queue<MODE>(t, v, in, out, wq, lane);
-}
-
-// ------------------------------------------------------------------------------------------
-// sample   (row A6; oracle: draw_direction + eval_pdf_one)
-// ------------------------------------------------------------------------------------------
-// Mitsuba 3's concentric square->disk map, lifted to the cosine-weighted hemisphere.
-__device__ __forceinline__ void cosine_hemisphere(float ux, float uy, float& x, float& y, float& z) {
-    const float sx = fmaf(2.f, ux, -1.f), sy = fmaf(2.f, uy, -1.f);
-    const bool q13 = fabsf(sx) < fabsf(sy);
-    const float r = q13 ? sy : sx, rp = q13 ? sx : sy;
-    float ph = 0.25f * __fdividef(rp, r);            // in units of pi
-    if (q13) ph = 0.5f - ph;
-    if (sx == 0.f && sy == 0.f) ph = 0.f;
-    float s, c;
-    sincospif(ph, &s, &c);
-    x = r * c; y = r * s;
-    // z^2 = 1 - x^2 - y^2 = 1 - r^2, factored so that it keeps full relative accuracy at the
-    // horizon (r -> 1), where the subtraction of squares would cancel in fp32
-    const float ar = fabsf(r);
-    z = sqrtf(fmaxf(0.f, (1.f - ar) * (1.f + ar)));
-}
-
-// Largest i in [0, nh-1] with row[i] <= u: per-lane bisection over the smem-resident row.
-__device__ __forceinline__ int search_lane(const float* row, int nh, float u) {
-    int lo = 0, hi = nh;
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (row[mid] <= u) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-// Same result, warp-cooperative: the warp walks its 32 queries; for each, every lane tests a
-// strided share of the row (conflict-free LDS) and __ballot_sync/__popc count the entries <= u.
-// row[] is non-decreasing, so that count - 1 is the bisection's answer.
-__device__ __forceinline__ int search_warp_coop(const float* cdf, int nh, int my_row, float my_u,
-                                                bool my_need, unsigned lane) {
-    int result = 0;
-    unsigned todo = __ballot_sync(0xffffffffu, my_need);
-    while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const int row_i = __shfl_sync(0xffffffffu, my_row, src);
-        const float u = __shfl_sync(0xffffffffu, my_u, src);
-        const float* row = cdf + row_i * (nh + 1);
-        int count = 0;
-        for (int base = 0; base < nh; base += 32) {   // entries 0..nh-1 (row[nh] = 1 > u always)
-            const int e = base + (int)lane;
-            const bool le = (e < nh) && (row[e] <= u);
-            count += __popc(__ballot_sync(0xffffffffu, le));
-        }
-        if ((int)lane == src) result = max(count - 1, 0);
-    }
-    return result;
-}
-
-struct SampleIn {
-    const float *wix, *wiy, *wiz, *u1, *u2x, *u2y;
-    const uint8_t* active;
-};
-struct SampleOut {
-    float *wox, *woy, *woz, *pdf, *wr, *wg, *wb;
-    uint32_t* lobe;
-};
-
-template <int VEC, int SEARCH>
-__global__ void __launch_bounds__(256) sample_kernel(const TableDev t, const SampleIn in, const int64_t ngroups,
-                                                     const SampleOut out) {
-    extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
-    stage_image(t, smem, t.image_full_floats);
-    const SmemView v = make_view(t, smem);
-    const unsigned lane = threadIdx.x & 31u;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    // SEARCH==1 uses warp collectives inside the loop, so the trip count must be warp-uniform.
-    const int64_t g0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    const int64_t gend = SEARCH ? ((ngroups + 31) / 32) * 32 : ngroups;
-    for (int64_t g = g0; g < gend; g += stride) {
-        const bool in_range = g < ngroups;
-        const int64_t gl = in_range ? g : 0;
-        const Pack<VEC> ax = load_stream<VEC>(in.wix, gl), ay = load_stream<VEC>(in.wiy, gl),
-                        az = load_stream<VEC>(in.wiz, gl), u1 = load_stream<VEC>(in.u1, gl),
-                        ux = load_stream<VEC>(in.u2x, gl), uy = load_stream<VEC>(in.u2y, gl);
-        const unsigned act = in_range ? load_active<VEC>(in.active, gl) : 0u;
-        Pack<VEC> bx, by, bz, pdf, wr, wg, wb;
-        uint32_t lobe[VEC];
-        int idx[VEC];
-        bool valid[VEC];
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) {
-            const bool ok = ((act >> q) & 1u) && az.v[q] > 0.f;
-            const bool spec = u1.v[q] < t.spec_weight;
-            lobe[q] = (ok && spec) ? 1u : 0u;
-            float x, y, z;
-            cosine_hemisphere(ux.v[q], uy.v[q], x, y, z);
-            const int j = max(min((int)(az.v[q] * (float)t.ni), t.ni - 1), 0);
-            int i;
-            if (SEARCH) i = search_warp_coop(v.cdf, t.nh, j, ux.v[q], ok && spec, lane);
-            else i = spec ? search_lane(v.cdf + j * (t.nh + 1), t.nh, ux.v[q]) : 0;
-            if (spec) {
-                const float* row = v.cdf + j * (t.nh + 1);
-                const float c0 = row[i], c1 = row[i + 1];
-                const float w = c1 - c0;
-                const float f = w > 0.f ? __fdividef(ux.v[q] - c0, w) : 0.5f;
-                const float m0 = v.medge[i], m1 = v.medge[i + 1];
-                const float m = fmaf(f, m1 - m0, m0);
-                const float ct = 1.f - m, st = sqrtf(m * (2.f - m));
-                float sp, cp;
-                sincospif(2.f * uy.v[q], &sp, &cp);
-                const float hx = st * cp, hy = st * sp, hz = ct;
-                const float c2 = 2.f * fmaf(ax.v[q], hx, fmaf(ay.v[q], hy, az.v[q] * hz));
-                x = fmaf(c2, hx, -ax.v[q]); y = fmaf(c2, hy, -ay.v[q]); z = fmaf(c2, hz, -az.v[q]);
-            }
-            bx.v[q] = x; by.v[q] = y; bz.v[q] = z;
-            valid[q] = ok && z > 0.f;
-            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], x, y, z);
-            const Bins b = compute_bins(t, v, ax.v[q], ay.v[q], az.v[q], x, y, z, h);
-            idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
-            pdf.v[q] = valid[q] ? pdf_from_bins(t, v, az.v[q], z, h, b.ih) : 0.f;
-            if (!ok) { bx.v[q] = 0.f; by.v[q] = 0.f; bz.v[q] = 0.f; }
-        }
-        float4 cell[VEC];
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) {
-            const bool good = valid[q] && pdf.v[q] > 0.f;
-            const float s = good ? __fdividef(bz.v[q], pdf.v[q]) : 0.f;
-            wr.v[q] = cell[q].x * s; wg.v[q] = cell[q].y * s; wb.v[q] = cell[q].z * s;
-            if (!good) pdf.v[q] = 0.f;
-        }
-        if (in_range) {
-            store_stream<VEC>(out.wox, g, bx); store_stream<VEC>(out.woy, g, by); store_stream<VEC>(out.woz, g, bz);
-            store_stream<VEC>(out.pdf, g, pdf);
-            store_stream<VEC>(out.wr, g, wr); store_stream<VEC>(out.wg, g, wg); store_stream<VEC>(out.wb, g, wb);
-            if (VEC == 4) {
-                reinterpret_cast<uint4*>(out.lobe)[g] = make_uint4(lobe[0], lobe[VEC > 1 ? 1 : 0],
-                                                                  lobe[VEC > 2 ? 2 : 0], lobe[VEC > 3 ? 3 : 0]);
-            } else {
-                out.lobe[g] = lobe[0];
-            }
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// backward   (row A10): grad_cells[idx] += (g_r, g_g, g_b) * cos(theta_o), one 16-byte RED
-// ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-                 : "memory");
-}
-
-struct BackwardIn {
-    QueryIn q;
-    const float *gr, *gg, *gb;
-};
-
-template <int VEC, int AGG>
-__global__ void __launch_bounds__(256) backward_kernel(const TableDev t, const BackwardIn in, const int64_t ngroups,
-                                                       float4* __restrict__ grad) {
-    extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
-    stage_image(t, smem, t.off_dens);
-    const SmemView v = make_view(t, smem);
-    const unsigned lane = threadIdx.x & 31u;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    const int64_t g0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    const int64_t gend = AGG ? ((ngroups + 31) / 32) * 32 : ngroups;
-    for (int64_t g = g0; g < gend; g += stride) {
-        const bool in_range = g < ngroups;
-        const int64_t gl = in_range ? g : 0;
-        const Pack<VEC> ax = load_stream<VEC>(in.q.wix, gl), ay = load_stream<VEC>(in.q.wiy, gl),
-                        az = load_stream<VEC>(in.q.wiz, gl), bx = load_stream<VEC>(in.q.wox, gl),
-                        by = load_stream<VEC>(in.q.woy, gl), bz = load_stream<VEC>(in.q.woz, gl),
-                        gr = load_stream<VEC>(in.gr, gl), gg = load_stream<VEC>(in.gg, gl),
-                        gb = load_stream<VEC>(in.gb, gl);
-        const unsigned act = in_range ? load_active<VEC>(in.q.active, gl) : 0u;
-        int idx[VEC];
-        bool valid[VEC];
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) {
-            valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
-            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
-            const Bins b = compute_bins(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h);
-            idx[q] = (b.ih * t.nd + b.id) * t.np + b.ip;
-        }
-        float bits[VEC];
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) bits[q] = __ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx[q] + 3]);
-#pragma unroll
-        for (int q = 0; q < VEC; ++q) {
-            const int m = (int)bits[q];
-            const float c = valid[q] ? bz.v[q] : 0.f;
-            float v0 = (m & 1) ? gr.v[q] * c : 0.f, v1 = (m & 2) ? gg.v[q] * c : 0.f,
-                  v2 = (m & 4) ? gb.v[q] * c : 0.f, v3 = valid[q] ? 1.f : 0.f;
-            bool emit = valid[q];
-            if (AGG) {
-                // lanes of this warp that hit the same cell fold into the lowest such lane
-                const int key = valid[q] ? idx[q] : -1 - (int)lane;
-                const unsigned peers = __match_any_sync(0xffffffffu, key);
-                if (__any_sync(0xffffffffu, peers & (peers - 1))) {
-                    if (peers == 0xffffffffu) {      // whole warp on one cell: butterfly
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) {
-                            v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o);
-                            v2 += __shfl_xor_sync(0xffffffffu, v2, o); v3 += __shfl_xor_sync(0xffffffffu, v3, o);
-                        }
-                        emit = emit && lane == 0;
-                    } else {
-                        const bool leader = (int)lane == __ffs(peers) - 1;
-                        unsigned rest = leader ? (peers & ~(1u << lane)) : 0u;
-                        const float m0 = v0, m1 = v1, m2 = v2, m3 = v3;
-                        while (__any_sync(0xffffffffu, rest != 0u)) {
-                            const int src = rest ? __ffs(rest) - 1 : (int)lane;
-                            const float a0 = __shfl_sync(0xffffffffu, m0, src), a1 = __shfl_sync(0xffffffffu, m1, src),
-                                        a2 = __shfl_sync(0xffffffffu, m2, src), a3 = __shfl_sync(0xffffffffu, m3, src);
-                            if (rest) { v0 += a0; v1 += a1; v2 += a2; v3 += a3; rest &= rest - 1; }
-                        }
-                        emit = emit && leader;
-                    }
-                }
-            }
-            if (emit) red_add_v4(grad + idx[q], v0, v1, v2, v3);
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// AoS variants for the Mitsuba 0.6 wavefront BSDF stage (float4 per query)
-// ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) eval_pdf_aos_kernel(const TableDev t, const float4* __restrict__ wi4,
-                                                           const float4* __restrict__ wo4, const int64_t n,
-                                                           float4* __restrict__ out4) {
-    extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
-    stage_image(t, smem, t.image_eval_floats);
-    const SmemView v = make_view(t, smem);
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n; g += stride) {
-        const float4 a = __ldcs(wi4 + g), b = __ldcs(wo4 + g);
-        const bool valid = a.z > 0.f && b.z > 0.f;
-        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, b.x, b.y, b.z);
-        const Bins bn = compute_bins(t, v, a.x, a.y, a.z, b.x, b.y, b.z, h);
-        const float4 cell = __ldg(&t.cells[(bn.ih * t.nd + bn.id) * t.np + bn.ip]);
-        const float c = valid ? b.z : 0.f;
-        const float p = valid ? pdf_from_bins(t, v, a.z, b.z, h, bn.ih) : 0.f;
-        __stcs(out4 + g, make_float4(cell.x * c, cell.y * c, cell.z * c, p));
-    }
-}
-
-__global__ void __launch_bounds__(256) sample_aos_kernel(const TableDev t, const float4* __restrict__ wi4,
-                                                         const float4* __restrict__ u4, const int64_t n,
-                                                         float4* __restrict__ wo4, float4* __restrict__ w4) {
-    extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
-    stage_image(t, smem, t.image_full_floats);
-    const SmemView v = make_view(t, smem);
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n; g += stride) {
-        const float4 a = __ldcs(wi4 + g), u = __ldcs(u4 + g);
-        const bool ok = a.z > 0.f;
-        const bool spec = u.x < t.spec_weight;
-        float x, y, z;
-        cosine_hemisphere(u.y, u.z, x, y, z);
-        if (spec) {
-            const int j = max(min((int)(a.z * (float)t.ni), t.ni - 1), 0);
-            const float* row = v.cdf + j * (t.nh + 1);
-            const int i = search_lane(row, t.nh, u.y);
-            const float c0 = row[i], w = row[i + 1] - c0;
-            const float f = w > 0.f ? __fdividef(u.y - c0, w) : 0.5f;
-            const float m0 = v.medge[i], m = fmaf(f, v.medge[i + 1] - m0, m0);
-            const float ct = 1.f - m, st = sqrtf(m * (2.f - m));
-            float sp, cp;
-            sincospif(2.f * u.z, &sp, &cp);
-            const float hx = st * cp, hy = st * sp, hz = ct;
-            const float c2 = 2.f * fmaf(a.x, hx, fmaf(a.y, hy, a.z * hz));
-            x = fmaf(c2, hx, -a.x); y = fmaf(c2, hy, -a.y); z = fmaf(c2, hz, -a.z);
-        }
-        const bool valid = ok && z > 0.f;
-        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, x, y, z);
-        const Bins bn = compute_bins(t, v, a.x, a.y, a.z, x, y, z, h);
-        const float4 cell = __ldg(&t.cells[(bn.ih * t.nd + bn.id) * t.np + bn.ip]);
-        float p = valid ? pdf_from_bins(t, v, a.z, z, h, bn.ih) : 0.f;
-        const bool good = valid && p > 0.f;
-        const float s = good ? __fdividef(z, p) : 0.f;
-        if (!good) p = 0.f;
-        if (!ok) { x = 0.f; y = 0.f; z = 0.f; }
-        __stcs(wo4 + g, make_float4(x, y, z, p));
-        __stcs(w4 + g, make_float4(cell.x * s, cell.y * s, cell.z * s, (ok && spec) ? 1.f : 0.f));
-    }
-}
-
-// ------------------------------------------------------------------------------------------
 // host: launch plumbing
 // ------------------------------------------------------------------------------------------
 static constexpr int kThreads = 256;
@@ -748,12 +240,15 @@ static int launch_persistent(const merl_table* t, K kernel, size_t smem, int64_t
 }
 
 static inline bool aligned(const void* p, size_t a) { return p == nullptr || ((uintptr_t)p % a) == 0; }
-static inline size_t eval_smem(const merl_table* t, bool pdf) {
-    return (size_t)(((pdf ? t->dev.image_eval_floats : t->dev.off_dens) + 3) & ~3) * sizeof(float);
+
+// Shared-memory layout of the streaming kernels: [table image, 128-byte rounded][warp queues].
+template <typename Op, int MINB>
+static int launch_op(const merl_table* t, const Op& op, int image_floats, int64_t ngroups, cudaStream_t s) {
+    const int img = (int)(((size_t)image_floats * sizeof(float) + 127) & ~(size_t)127);
+    return launch_persistent(t, stream_kernel<Op, MINB>, (size_t)img + kQueueBytes, ngroups, s, t->dev, op, ngroups,
+                             img);
 }
-static inline size_t full_smem(const merl_table* t) {
-    return (size_t)((t->dev.image_full_floats + 3) & ~3) * sizeof(float);
-}
+static inline int eval_floats(const merl_table* t, bool pdf) { return pdf ? t->dev.image_eval_floats : t->dev.off_dens; }
 
 static QueryIn offset_in(QueryIn q, int64_t o) {
     q.wix += o; q.wiy += o; q.wiz += o; q.wox += o; q.woy += o; q.woz += o;
@@ -765,26 +260,23 @@ static QueryOut offset_out(QueryOut q, int64_t o) {
     return q;
 }
 
-// Shared-memory layout of the streaming kernels: [table image, 128-byte rounded][warp queues].
-static inline int image_bytes(size_t image) { return (int)((image + 127) & ~(size_t)127); }
-
+// Four queries per lane when every buffer allows 16-byte transactions; the (< 4 query) tail and
+// unaligned buffers take the one-query-per-lane instantiation of the same op.
 template <int MODE>
 static int run_query_mode(const merl_table* t, const QueryIn& in, int64_t n, const QueryOut& out, cudaStream_t s) {
-    const int img = image_bytes(eval_smem(t, MODE == MODE_PDF || MODE == MODE_EVAL_PDF));
-    const size_t smem = (size_t)img + kQueueBytes;
+    const int fl = eval_floats(t, MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
     const bool vec = aligned(in.wix, 16) && aligned(in.wiy, 16) && aligned(in.wiz, 16) && aligned(in.wox, 16) &&
                      aligned(in.woy, 16) && aligned(in.woz, 16) && aligned(in.active, 4) && aligned(out.r, 16) &&
                      aligned(out.g, 16) && aligned(out.b, 16) && aligned(out.pdf, 16) && aligned(out.idx, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int64_t ng = n / 4;
-        const int rc = launch_persistent(t, query_kernel<MODE, 4, 3>, smem, ng, s, t->dev, in, ng, out, img);
+        const int rc = launch_op<QueryOp<MODE, 4>, 3>(t, QueryOp<MODE, 4>{in, out}, fl, n / 4, s);
         if (rc) return rc;
-        done = ng * 4;
+        done = (n / 4) * 4;
     }
     if (done < n)
-        return launch_persistent(t, query_kernel<MODE, 1, 4>, smem, n - done, s, t->dev, offset_in(in, done), n - done,
-                                 offset_out(out, done), img);
+        return launch_op<QueryOp<MODE, 1>, 4>(t, QueryOp<MODE, 1>{offset_in(in, done), offset_out(out, done)}, fl,
+                                              n - done, s);
     return MERL_OK;
 }
 
@@ -874,6 +366,8 @@ static int build_table(const double* planar, const merl_table_params_t* pin, int
     d.kd = (float)(p.nd * 2.0 / PI);
     d.kp = (float)(p.np / PI);
     d.spec_weight = p.spec_weight;
+    d.search_step = 1;
+    while (d.search_step * 2 <= p.nh - 1) d.search_step *= 2;
 
     // bin edges in double (host libm), then rounded to fp32 for tier 1
     const int n64 = (p.nh + 1) + (p.nd + 1) + 2 * (p.np + 1) + (p.nh + 1);
@@ -1004,8 +498,8 @@ extern "C" int merl_table_info(const merl_table_t* t, merl_table_info_t* o) {
     o->d_cdf = t->d_image + t->dev.off_cdf;
     o->d_dens = t->d_image + t->dev.off_dens;
     o->spec_weight = t->dev.spec_weight;
-    o->smem_eval_bytes = (int32_t)eval_smem(t, true);
-    o->smem_sample_bytes = (int32_t)full_smem(t);
+    o->smem_eval_bytes = (int32_t)(t->dev.image_eval_floats * sizeof(float)) + kQueueBytes;
+    o->smem_sample_bytes = (int32_t)(t->dev.image_full_floats * sizeof(float)) + kQueueBytes;
     return MERL_OK;
 }
 
@@ -1081,14 +575,14 @@ extern "C" int merl_eval_pdf(const merl_table_t* t, const float* wix, const floa
 
 template <int SEARCH>
 static int run_sample(const merl_table* t, SampleIn in, int64_t n, SampleOut out, cudaStream_t s) {
-    const size_t smem = full_smem(t);
+    const int fl = t->dev.image_full_floats;
     const bool vec = aligned(in.wix, 16) && aligned(in.wiy, 16) && aligned(in.wiz, 16) && aligned(in.u1, 16) &&
                      aligned(in.u2x, 16) && aligned(in.u2y, 16) && aligned(in.active, 4) && aligned(out.wox, 16) &&
                      aligned(out.woy, 16) && aligned(out.woz, 16) && aligned(out.pdf, 16) && aligned(out.wr, 16) &&
                      aligned(out.wg, 16) && aligned(out.wb, 16) && aligned(out.lobe, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_persistent(t, sample_kernel<4, SEARCH>, smem, n / 4, s, t->dev, in, n / 4, out);
+        const int rc = launch_op<SampleOp<4, SEARCH>, 2>(t, SampleOp<4, SEARCH>{in, out}, fl, n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;
     }
@@ -1097,7 +591,7 @@ static int run_sample(const merl_table* t, SampleIn in, int64_t n, SampleOut out
         if (in.active) in.active += done;
         out.wox += done; out.woy += done; out.woz += done; out.pdf += done;
         out.wr += done; out.wg += done; out.wb += done; out.lobe += done;
-        return launch_persistent(t, sample_kernel<1, SEARCH>, smem, n - done, s, t->dev, in, n - done, out);
+        return launch_op<SampleOp<1, SEARCH>, 3>(t, SampleOp<1, SEARCH>{in, out}, fl, n - done, s);
     }
     return MERL_OK;
 }
@@ -1117,23 +611,30 @@ extern "C" int merl_sample(const merl_table_t* t, const float* wix, const float*
                                 : run_sample<0>(t, in, n, out, (cudaStream_t)stream);
 }
 
+struct BackwardIn {
+    QueryIn q;
+    const float *gr, *gg, *gb;
+};
+
 template <int AGG>
 static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* grad, cudaStream_t s) {
-    const size_t smem = eval_smem(t, false);
+    const int fl = t->dev.off_dens;
     const QueryIn& q = in.q;
     const bool vec = aligned(q.wix, 16) && aligned(q.wiy, 16) && aligned(q.wiz, 16) && aligned(q.wox, 16) &&
                      aligned(q.woy, 16) && aligned(q.woz, 16) && aligned(q.active, 4) && aligned(in.gr, 16) &&
                      aligned(in.gg, 16) && aligned(in.gb, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_persistent(t, backward_kernel<4, AGG>, smem, n / 4, s, t->dev, in, n / 4, grad);
+        const int rc = launch_op<BackwardOp<4, AGG>, 2>(t, BackwardOp<4, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl,
+                                                        n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;
     }
     if (done < n) {
         in.q = offset_in(in.q, done);
         in.gr += done; in.gg += done; in.gb += done;
-        return launch_persistent(t, backward_kernel<1, AGG>, smem, n - done, s, t->dev, in, n - done, grad);
+        return launch_op<BackwardOp<1, AGG>, 3>(t, BackwardOp<1, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done,
+                                                s);
     }
     return MERL_OK;
 }
@@ -1159,9 +660,9 @@ extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const 
     if (!aligned(wi4, 16) || !aligned(wo4, 16) || !aligned(out4, 16))
         return fail(MERL_ERR_ARG, "AoS buffers must be 16-byte aligned");
     DeviceGuard gd(t->device);
-    return launch_persistent(t, eval_pdf_aos_kernel, eval_smem(t, true), n, (cudaStream_t)stream, t->dev,
-                             reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(wo4), n,
-                             reinterpret_cast<float4*>(out4));
+    const EvalPdfAosOp op{reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(wo4),
+                          reinterpret_cast<float4*>(out4)};
+    return launch_op<EvalPdfAosOp, 4>(t, op, t->dev.image_eval_floats, n, (cudaStream_t)stream);
 }
 
 extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const float* u4, int64_t n, float* wo4_out,
@@ -1170,9 +671,9 @@ extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const fl
     if (!aligned(wi4, 16) || !aligned(u4, 16) || !aligned(wo4_out, 16) || !aligned(weight4_out, 16))
         return fail(MERL_ERR_ARG, "AoS buffers must be 16-byte aligned");
     DeviceGuard gd(t->device);
-    return launch_persistent(t, sample_aos_kernel, full_smem(t), n, (cudaStream_t)stream, t->dev,
-                             reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(u4), n,
-                             reinterpret_cast<float4*>(wo4_out), reinterpret_cast<float4*>(weight4_out));
+    const SampleAosOp op{reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(u4),
+                         reinterpret_cast<float4*>(wo4_out), reinterpret_cast<float4*>(weight4_out)};
+    return launch_op<SampleAosOp, 3>(t, op, t->dev.image_full_floats, n, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------

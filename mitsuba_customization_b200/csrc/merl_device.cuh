@@ -39,6 +39,7 @@ struct TableDev {
     float kd;                // nd*2/pi
     float kp;                // np/pi
     float spec_weight;
+    int search_step;         // largest power of two <= nh-1: first stride of the CDF row search
 };
 
 // Views into the staged shared-memory image.

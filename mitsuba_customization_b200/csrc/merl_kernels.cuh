@@ -1,0 +1,561 @@
+// merl_kernels.cuh -- the streaming kernels of libmerl_b200 (sm_100a).
+//
+// Every batched entry point (bins / eval / pdf / eval_pdf / sample / backward, SoA and AoS) is one
+// instantiation of stream_kernel<Op>: a persistent grid-stride kernel sized to the SM count that
+//   - stages the per-table edge/density/CDF image in shared memory once per CTA,
+//   - streams queries with 16-byte evict-first loads and stores (SoA: four queries per lane),
+//   - gathers one float4 per query from the L2-resident table,
+//   - runs ONLY tier 1 of the bin computation (merl_device.cuh) in the loop, branch-free, and
+//     defers queries whose tier-1 decision was inside its error margin to a warp-private queue
+//     in shared memory; Op::redo() re-does those exactly (tiers 2-3) and overwrites their outputs.
+// Included exactly once, by merl_b200.cu.
+#pragma once
+#include "merl_device.cuh"
+#include "merl_slow.cuh"
+
+namespace merl {
+
+// ------------------------------------------------------------------------------------------
+// streamed SoA access: VEC consecutive queries per thread, evict-first transactions
+// ------------------------------------------------------------------------------------------
+template <int VEC> struct Pack { float v[VEC]; };
+
+template <int VEC> __device__ __forceinline__ Pack<VEC> load_stream(const float* p, int64_t g);
+template <> __device__ __forceinline__ Pack<1> load_stream<1>(const float* p, int64_t g) {
+    Pack<1> r; r.v[0] = __ldcs(p + g); return r;
+}
+template <> __device__ __forceinline__ Pack<4> load_stream<4>(const float* p, int64_t g) {
+    const float4 f = __ldcs(reinterpret_cast<const float4*>(p) + g);
+    Pack<4> r; r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w; return r;
+}
+template <int VEC> __device__ __forceinline__ void store_stream(float* p, int64_t g, const Pack<VEC>& a);
+template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g, const Pack<1>& a) {
+    __stcs(p + g, a.v[0]);
+}
+template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g, const Pack<4>& a) {
+    __stcs(reinterpret_cast<float4*>(p) + g, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
+}
+template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
+template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
+    return p ? (p[g] != 0) : 1u;
+}
+template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p, int64_t g) {
+    if (!p) return 0xFu;
+    const uint32_t w = __ldcs(reinterpret_cast<const uint32_t*>(p) + g);
+    return ((w & 0xFFu) != 0) | (((w >> 8) & 0xFFu) != 0) << 1 | (((w >> 16) & 0xFFu) != 0) << 2 |
+           ((w >> 24) != 0) << 3;
+}
+
+// ------------------------------------------------------------------------------------------
+// Deferred exactness.  The streaming loop runs tier 1 only (branch-free, no fp64, ~40 fewer
+// registers, and the four queries a lane holds interleave).  A query whose tier-1 decision was
+// inside its error margin (~1.3e-3 of uniform queries) is appended to the warp's private queue
+// in shared memory and re-done exactly when the queue could overflow or the warp runs out of
+// work.  The redo overwrites that query's outputs, so results equal the all-tiers computation
+// for every input, including adversarial batches in which every query is uncertain (the warp
+// then flushes every iteration: slow, still exact).  No scratch memory, no second launch.
+// ------------------------------------------------------------------------------------------
+constexpr int kThreadsPerCta = 256;
+constexpr int kWarpsPerCta = kThreadsPerCta / 32;
+constexpr int kQueueCap = 256;                      // entries per warp (8 B each)
+constexpr int kQueueBytes = kWarpsPerCta * (kQueueCap * 8 + 8);
+
+struct WarpQueue {
+    int64_t* items;   // [kQueueCap] absolute query indices
+    int* count;
+};
+__device__ __forceinline__ WarpQueue warp_queue(char* base, int warp) {
+    WarpQueue q;
+    q.items = reinterpret_cast<int64_t*>(base) + warp * kQueueCap;
+    q.count = reinterpret_cast<int*>(base + kWarpsPerCta * kQueueCap * 8) + warp * 2;
+    return q;
+}
+
+template <typename Op>
+__device__ __forceinline__ void flush_queue(const Op& op, const TableDev& t, const SmemView& v, const WarpQueue& wq,
+                                            const int lane) {
+    __syncwarp();   // orders this warp's streaming stores before the redo stores
+    const int n = *reinterpret_cast<volatile int*>(wq.count);
+    for (int e = lane; e < n; e += 32) op.redo(t, v, wq.items[e]);
+    __syncwarp();
+    if (lane == 0) *reinterpret_cast<volatile int*>(wq.count) = 0;
+    __syncwarp();
+}
+
+// Op interface:
+//   static constexpr int kVec       queries per lane and iteration
+//   int image_floats(t)             floats of the table image the op needs in shared memory
+//   unsigned hot(t, v, g, in_range, lane)   tier-1 pass over group g (called by every lane of the
+//                                   warp, so ops may use warp collectives); returns bit q set
+//                                   when query g*kVec+q must be re-done
+//   void redo(t, v, i)              exact pass over the single query i
+template <typename Op, int MINB>
+__global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const TableDev t, const Op op,
+                                                                      const int64_t ngroups, const int image_bytes) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const WarpQueue wq = warp_queue(reinterpret_cast<char*>(smem4) + image_bytes, warp);
+    if (lane == 0) *wq.count = 0;
+    stage_image(t, smem, op.image_floats(t));   // ends with __syncthreads()
+    const SmemView v = make_view(t, smem);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // warp-uniform trip count: flush and some ops use warp-level synchronisation
+    for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
+        const int64_t g = g0 + lane;
+        const unsigned m = op.hot(t, v, g, g < ngroups, lane);
+        if (m) {
+#pragma unroll
+            for (int q = 0; q < Op::kVec; ++q)
+                if ((m >> q) & 1u) wq.items[atomicAdd(wq.count, 1)] = g * Op::kVec + q;
+        }
+        __syncwarp();
+        if (*reinterpret_cast<volatile int*>(wq.count) > kQueueCap - 32 * Op::kVec) flush_queue(op, t, v, wq, lane);
+    }
+    flush_queue(op, t, v, wq, lane);
+}
+
+// pdf of the two-lobe sampler given the theta_h bin (row A5; oracle: eval_pdf_one).  Branch-free:
+// the density is read for every lane (clamped slice index) and selected.
+__device__ __forceinline__ float pdf_from_bins(const TableDev& t, const SmemView& v, float az, float bz,
+                                               const HalfDiff& h, int ih) {
+    const int j = max(min((int)(az * (float)t.ni), t.ni - 1), 0);
+    const float p = (1.f - t.spec_weight) * bz * 0.318309886f;
+    const float ps = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
+    return h.A > 0.f ? ps : p;
+}
+__device__ __forceinline__ int flat_index(const TableDev& t, const Bins& b) { return (b.ih * t.nd + b.id) * t.np + b.ip; }
+
+// ------------------------------------------------------------------------------------------
+// bins / eval / pdf / eval_pdf   (rows A1-A5)
+// ------------------------------------------------------------------------------------------
+enum QueryMode { MODE_BINS = 0, MODE_EVAL = 1, MODE_PDF = 2, MODE_EVAL_PDF = 3 };
+
+struct QueryIn {
+    const float *wix, *wiy, *wiz, *wox, *woy, *woz;
+    const uint8_t* active;
+};
+struct QueryOut {
+    float *r, *g, *b, *pdf;
+    int32_t* idx;
+};
+
+template <int MODE, int VEC>
+struct QueryOp {
+    static constexpr int kVec = VEC;
+    static constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
+    static constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
+    QueryIn in;
+    QueryOut out;
+
+    __device__ __forceinline__ int image_floats(const TableDev& t) const { return kPdf ? t.image_eval_floats : t.off_dens; }
+
+    __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                            const int) const {
+        if (!in_range) return 0u;
+        const Pack<VEC> ax = load_stream<VEC>(in.wix, g), ay = load_stream<VEC>(in.wiy, g),
+                        az = load_stream<VEC>(in.wiz, g), bx = load_stream<VEC>(in.wox, g),
+                        by = load_stream<VEC>(in.woy, g), bz = load_stream<VEC>(in.woz, g);
+        const unsigned act = load_active<VEC>(in.active, g);
+        int idx[VEC];
+        Pack<VEC> pdf;
+        bool valid[VEC];
+        unsigned uncmask = 0;
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
+            unsigned unc;
+            int kc[3];
+            const Bins b = compute_bins_fast(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h, unc, kc);
+            uncmask |= (unsigned)((unc != 0u) & valid[q]) << q;
+            idx[q] = flat_index(t, b);
+            if (kPdf) {
+                const float pq = pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih);
+                pdf.v[q] = valid[q] ? pq : 0.f;
+            }
+        }
+        if (kEval) {
+            float4 cell[VEC];
+#pragma unroll
+            for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
+            Pack<VEC> r, gg, bb;
+#pragma unroll
+            for (int q = 0; q < VEC; ++q) {
+                const float c = valid[q] ? bz.v[q] : 0.f;
+                r.v[q] = cell[q].x * c; gg.v[q] = cell[q].y * c; bb.v[q] = cell[q].z * c;
+            }
+            store_stream<VEC>(out.r, g, r);
+            store_stream<VEC>(out.g, g, gg);
+            store_stream<VEC>(out.b, g, bb);
+        }
+        if (kPdf) store_stream<VEC>(out.pdf, g, pdf);
+        if (MODE == MODE_BINS) {
+            if (VEC == 4) {
+                reinterpret_cast<int4*>(out.idx)[g] =
+                    make_int4(valid[0] ? idx[0] : -1, valid[VEC > 1 ? 1 : 0] ? idx[VEC > 1 ? 1 : 0] : -1,
+                              valid[VEC > 2 ? 2 : 0] ? idx[VEC > 2 ? 2 : 0] : -1,
+                              valid[VEC > 3 ? 3 : 0] ? idx[VEC > 3 ? 3 : 0] : -1);
+            } else {
+#pragma unroll
+                for (int q = 0; q < VEC; ++q) out.idx[g * VEC + q] = valid[q] ? idx[q] : -1;
+            }
+        }
+        return uncmask;
+    }
+
+    // only queries that were valid and uncertain get here
+    __device__ __forceinline__ void redo(const TableDev& t, const SmemView& v, const int64_t i) const {
+        const float ax = in.wix[i], ay = in.wiy[i], az = in.wiz[i], bx = in.wox[i], by = in.woy[i], bz = in.woz[i];
+        const HalfDiff h = half_diff_setup(ax, ay, az, bx, by, bz);
+        const Bins b = compute_bins(t, v, ax, ay, az, bx, by, bz, h);
+        const int idx = flat_index(t, b);
+        if (kEval) {
+            const float4 cell = __ldg(&t.cells[idx]);
+            out.r[i] = cell.x * bz; out.g[i] = cell.y * bz; out.b[i] = cell.z * bz;
+        }
+        if (kPdf) out.pdf[i] = pdf_from_bins(t, v, az, bz, h, b.ih);
+        if (MODE == MODE_BINS) out.idx[i] = idx;
+    }
+};
+
+// ------------------------------------------------------------------------------------------
+// sample   (row A6; oracle: draw_direction + eval_pdf_one)
+// ------------------------------------------------------------------------------------------
+// Mitsuba 3's concentric square->disk map, lifted to the cosine-weighted hemisphere.
+__device__ __forceinline__ void cosine_hemisphere(float ux, float uy, float& x, float& y, float& z) {
+    const float sx = fmaf(2.f, ux, -1.f), sy = fmaf(2.f, uy, -1.f);
+    const bool q13 = fabsf(sx) < fabsf(sy);
+    const float r = q13 ? sy : sx, rp = q13 ? sx : sy;
+    float ph = 0.25f * __fdividef(rp, r);            // in units of pi
+    if (q13) ph = 0.5f - ph;
+    if (sx == 0.f && sy == 0.f) ph = 0.f;
+    float s, c;
+    sincospif(ph, &s, &c);
+    x = r * c; y = r * s;
+    // z^2 = 1 - x^2 - y^2 = 1 - r^2, factored so that it keeps full relative accuracy at the
+    // horizon (r -> 1), where the subtraction of squares would cancel in fp32
+    const float ar = fabsf(r);
+    z = sqrtf(fmaxf(0.f, (1.f - ar) * (1.f + ar)));
+}
+
+// Largest i in [0, nh-1] with row[i] <= u (row[0] = 0).  Per-lane, fixed trip count (no
+// divergence): descending power-of-two strides over the smem-resident row.
+__device__ __forceinline__ int search_lane(const float* row, int nh, int step0, float u) {
+    int lo = 0;
+    for (int step = step0; step > 0; step >>= 1) {
+        const int m = lo + step;
+        const float e = row[min(m, nh - 1)];
+        lo = (m < nh && e <= u) ? m : lo;
+    }
+    return lo;
+}
+// Same result, warp-cooperative: the warp walks its queries; for each, every lane tests a
+// strided share of the row (conflict-free LDS) and __ballot_sync/__popc count the entries <= u.
+// row[] is non-decreasing, so that count - 1 is the bisection's answer.
+__device__ __forceinline__ int search_warp_coop(const float* cdf, int nh, int my_row, float my_u,
+                                                bool my_need, unsigned lane) {
+    int result = 0;
+    unsigned todo = __ballot_sync(0xffffffffu, my_need);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int row_i = __shfl_sync(0xffffffffu, my_row, src);
+        const float u = __shfl_sync(0xffffffffu, my_u, src);
+        const float* row = cdf + row_i * (nh + 1);
+        int count = 0;
+        for (int base = 0; base < nh; base += 32) {   // entries 0..nh-1 (row[nh] = 1 > u always)
+            const int e = base + (int)lane;
+            const bool le = (e < nh) && (row[e] <= u);
+            count += __popc(__ballot_sync(0xffffffffu, le));
+        }
+        if ((int)lane == src) result = max(count - 1, 0);
+    }
+    return result;
+}
+
+// wo of the tabulated half-vector lobe: theta_h bin i of slice j, solid-angle-uniform inside the
+// bin, phi_h = 2 pi uy; wo = reflect(wi, h).
+__device__ __forceinline__ void spec_direction(const SmemView& v, const float* row, int i, float ax, float ay,
+                                               float az, float ux, float uy, float& x, float& y, float& z) {
+    const float c0 = row[i], c1 = row[i + 1];
+    const float w = c1 - c0;
+    const float f = w > 0.f ? __fdividef(ux - c0, w) : 0.5f;
+    const float m0 = v.medge[i], m1 = v.medge[i + 1];
+    const float m = fmaf(f, m1 - m0, m0);
+    const float ct = 1.f - m, st = sqrtf(m * (2.f - m));
+    float sp, cp;
+    sincospif(2.f * uy, &sp, &cp);
+    const float hx = st * cp, hy = st * sp, hz = ct;
+    const float c2 = 2.f * fmaf(ax, hx, fmaf(ay, hy, az * hz));
+    x = fmaf(c2, hx, -ax); y = fmaf(c2, hy, -ay); z = fmaf(c2, hz, -az);
+}
+
+struct SampleIn {
+    const float *wix, *wiy, *wiz, *u1, *u2x, *u2y;
+    const uint8_t* active;
+};
+struct SampleOut {
+    float *wox, *woy, *woz, *pdf, *wr, *wg, *wb;
+    uint32_t* lobe;
+};
+
+template <int VEC, int SEARCH>
+struct SampleOp {
+    static constexpr int kVec = VEC;
+    SampleIn in;
+    SampleOut out;
+
+    __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.image_full_floats; }
+
+    __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                            const int lane) const {
+        if (!SEARCH && !in_range) return 0u;
+        const int64_t gl = in_range ? g : 0;
+        const Pack<VEC> ax = load_stream<VEC>(in.wix, gl), ay = load_stream<VEC>(in.wiy, gl),
+                        az = load_stream<VEC>(in.wiz, gl), u1 = load_stream<VEC>(in.u1, gl),
+                        ux = load_stream<VEC>(in.u2x, gl), uy = load_stream<VEC>(in.u2y, gl);
+        const unsigned act = in_range ? load_active<VEC>(in.active, gl) : 0u;
+        Pack<VEC> bx, by, bz, pdf, wr, wg, wb;
+        uint32_t lobe[VEC];
+        int idx[VEC];
+        bool valid[VEC];
+        unsigned uncmask = 0;
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            const bool ok = ((act >> q) & 1u) && az.v[q] > 0.f;
+            const bool spec = u1.v[q] < t.spec_weight;
+            lobe[q] = (ok && spec) ? 1u : 0u;
+            float x, y, z, sx, sy, sz;
+            cosine_hemisphere(ux.v[q], uy.v[q], x, y, z);
+            const int j = max(min((int)(az.v[q] * (float)t.ni), t.ni - 1), 0);
+            const float* row = v.cdf + j * (t.nh + 1);
+            const int i = SEARCH ? search_warp_coop(v.cdf, t.nh, j, ux.v[q], ok && spec, (unsigned)lane)
+                                 : search_lane(row, t.nh, t.search_step, ux.v[q]);
+            spec_direction(v, row, i, ax.v[q], ay.v[q], az.v[q], ux.v[q], uy.v[q], sx, sy, sz);
+            x = spec ? sx : x; y = spec ? sy : y; z = spec ? sz : z;
+            valid[q] = ok && z > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], x, y, z);
+            unsigned unc;
+            int kc[3];
+            const Bins b = compute_bins_fast(t, v, ax.v[q], ay.v[q], az.v[q], x, y, z, h, unc, kc);
+            uncmask |= (unsigned)((unc != 0u) & valid[q]) << q;
+            idx[q] = flat_index(t, b);
+            const float pq = pdf_from_bins(t, v, az.v[q], z, h, b.ih);
+            pdf.v[q] = valid[q] ? pq : 0.f;
+            bx.v[q] = ok ? x : 0.f; by.v[q] = ok ? y : 0.f; bz.v[q] = ok ? z : 0.f;
+        }
+        float4 cell[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) cell[q] = __ldg(&t.cells[idx[q]]);
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            const bool good = valid[q] && pdf.v[q] > 0.f;
+            const float s = good ? __fdividef(bz.v[q], pdf.v[q]) : 0.f;
+            wr.v[q] = cell[q].x * s; wg.v[q] = cell[q].y * s; wb.v[q] = cell[q].z * s;
+            pdf.v[q] = good ? pdf.v[q] : 0.f;
+        }
+        if (in_range) {
+            store_stream<VEC>(out.wox, g, bx); store_stream<VEC>(out.woy, g, by); store_stream<VEC>(out.woz, g, bz);
+            store_stream<VEC>(out.pdf, g, pdf);
+            store_stream<VEC>(out.wr, g, wr); store_stream<VEC>(out.wg, g, wg); store_stream<VEC>(out.wb, g, wb);
+            if (VEC == 4) {
+                reinterpret_cast<uint4*>(out.lobe)[g] = make_uint4(lobe[0], lobe[VEC > 1 ? 1 : 0],
+                                                                  lobe[VEC > 2 ? 2 : 0], lobe[VEC > 3 ? 3 : 0]);
+            } else {
+                out.lobe[g] = lobe[0];
+            }
+        }
+        return in_range ? uncmask : 0u;
+    }
+
+    // wo and lobe of an uncertain query are already final (they do not depend on the bins);
+    // only pdf and weight are re-derived from the exact bins of (wi, stored wo).
+    __device__ __forceinline__ void redo(const TableDev& t, const SmemView& v, const int64_t i) const {
+        const float ax = in.wix[i], ay = in.wiy[i], az = in.wiz[i];
+        const float x = __ldcg(out.wox + i), y = __ldcg(out.woy + i), z = __ldcg(out.woz + i);
+        const HalfDiff h = half_diff_setup(ax, ay, az, x, y, z);
+        const Bins b = compute_bins(t, v, ax, ay, az, x, y, z, h);
+        const float4 cell = __ldg(&t.cells[flat_index(t, b)]);
+        float p = pdf_from_bins(t, v, az, z, h, b.ih);
+        const bool good = p > 0.f;
+        const float s = good ? __fdividef(z, p) : 0.f;
+        out.pdf[i] = good ? p : 0.f;
+        out.wr[i] = cell.x * s; out.wg[i] = cell.y * s; out.wb[i] = cell.z * s;
+    }
+};
+
+// ------------------------------------------------------------------------------------------
+// backward   (row A10): grad_cells[idx] += (g_r, g_g, g_b) * cos(theta_o), one 16-byte RED
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+template <int VEC, int AGG>
+struct BackwardOp {
+    static constexpr int kVec = VEC;
+    QueryIn q;
+    const float *gr, *gg, *gb;
+    float4* grad;
+
+    __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.off_dens; }
+
+    __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                            const int lane) const {
+        if (!AGG && !in_range) return 0u;
+        const int64_t gl = in_range ? g : 0;
+        const Pack<VEC> ax = load_stream<VEC>(q.wix, gl), ay = load_stream<VEC>(q.wiy, gl),
+                        az = load_stream<VEC>(q.wiz, gl), bx = load_stream<VEC>(q.wox, gl),
+                        by = load_stream<VEC>(q.woy, gl), bz = load_stream<VEC>(q.woz, gl),
+                        cr = load_stream<VEC>(gr, gl), cg = load_stream<VEC>(gg, gl), cb = load_stream<VEC>(gb, gl);
+        const unsigned act = in_range ? load_active<VEC>(q.active, gl) : 0u;
+        int idx[VEC];
+        bool emit[VEC];
+        unsigned uncmask = 0;
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const bool valid = ((act >> k) & 1u) && az.v[k] > 0.f && bz.v[k] > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[k], ay.v[k], az.v[k], bx.v[k], by.v[k], bz.v[k]);
+            unsigned unc;
+            int kc[3];
+            const Bins b = compute_bins_fast(t, v, ax.v[k], ay.v[k], az.v[k], bx.v[k], by.v[k], bz.v[k], h, unc, kc);
+            uncmask |= (unsigned)((unc != 0u) & valid) << k;
+            emit[k] = valid & (unc == 0u);   // an uncertain query adds nothing here: redo() does its RED
+            idx[k] = flat_index(t, b);
+        }
+        float bits[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) bits[k] = __ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx[k] + 3]);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const int m = (int)bits[k];
+            const float c = emit[k] ? bz.v[k] : 0.f;
+            float v0 = (m & 1) ? cr.v[k] * c : 0.f, v1 = (m & 2) ? cg.v[k] * c : 0.f,
+                  v2 = (m & 4) ? cb.v[k] * c : 0.f, v3 = emit[k] ? 1.f : 0.f;
+            bool em = emit[k];
+            if (AGG) {
+                // lanes of this warp that hit the same cell fold into the lowest such lane
+                const int key = em ? idx[k] : -1 - lane;
+                const unsigned peers = __match_any_sync(0xffffffffu, key);
+                if (__any_sync(0xffffffffu, peers & (peers - 1))) {
+                    if (peers == 0xffffffffu) {      // whole warp on one cell: butterfly
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+                            v2 += __shfl_xor_sync(0xffffffffu, v2, o); v3 += __shfl_xor_sync(0xffffffffu, v3, o);
+                        }
+                        em = em && lane == 0;
+                    } else {
+                        const bool leader = lane == __ffs(peers) - 1;
+                        unsigned rest = leader ? (peers & ~(1u << lane)) : 0u;
+                        const float m0 = v0, m1 = v1, m2 = v2, m3 = v3;
+                        while (__any_sync(0xffffffffu, rest != 0u)) {
+                            const int src = rest ? __ffs(rest) - 1 : lane;
+                            const float a0 = __shfl_sync(0xffffffffu, m0, src), a1 = __shfl_sync(0xffffffffu, m1, src),
+                                        a2 = __shfl_sync(0xffffffffu, m2, src), a3 = __shfl_sync(0xffffffffu, m3, src);
+                            if (rest) { v0 += a0; v1 += a1; v2 += a2; v3 += a3; rest &= rest - 1; }
+                        }
+                        em = em && leader;
+                    }
+                }
+            }
+            if (em) red_add_v4(grad + idx[k], v0, v1, v2, v3);
+        }
+        return in_range ? uncmask : 0u;
+    }
+
+    __device__ __forceinline__ void redo(const TableDev& t, const SmemView& v, const int64_t i) const {
+        const float ax = q.wix[i], ay = q.wiy[i], az = q.wiz[i], bx = q.wox[i], by = q.woy[i], bz = q.woz[i];
+        const HalfDiff h = half_diff_setup(ax, ay, az, bx, by, bz);
+        const Bins b = compute_bins(t, v, ax, ay, az, bx, by, bz, h);
+        const int idx = flat_index(t, b);
+        const int m = (int)__ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx + 3]);
+        red_add_v4(grad + idx, (m & 1) ? gr[i] * bz : 0.f, (m & 2) ? gg[i] * bz : 0.f, (m & 4) ? gb[i] * bz : 0.f, 1.f);
+    }
+};
+
+// ------------------------------------------------------------------------------------------
+// AoS variants for the Mitsuba 0.6 wavefront BSDF stage (one float4 per query and buffer)
+// ------------------------------------------------------------------------------------------
+struct EvalPdfAosOp {
+    static constexpr int kVec = 1;
+    const float4 *wi4, *wo4;
+    float4* out4;
+
+    __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.image_eval_floats; }
+
+    __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                            const int) const {
+        if (!in_range) return 0u;
+        const float4 a = __ldcs(wi4 + g), b = __ldcs(wo4 + g);
+        const bool valid = a.z > 0.f && b.z > 0.f;
+        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, b.x, b.y, b.z);
+        unsigned unc;
+        int kc[3];
+        const Bins bn = compute_bins_fast(t, v, a.x, a.y, a.z, b.x, b.y, b.z, h, unc, kc);
+        const float4 cell = __ldg(&t.cells[flat_index(t, bn)]);
+        const float c = valid ? b.z : 0.f;
+        const float pq = pdf_from_bins(t, v, a.z, b.z, h, bn.ih);
+        __stcs(out4 + g, make_float4(cell.x * c, cell.y * c, cell.z * c, valid ? pq : 0.f));
+        return (unsigned)((unc != 0u) & valid);
+    }
+    __device__ __forceinline__ void redo(const TableDev& t, const SmemView& v, const int64_t i) const {
+        const float4 a = wi4[i], b = wo4[i];
+        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, b.x, b.y, b.z);
+        const Bins bn = compute_bins(t, v, a.x, a.y, a.z, b.x, b.y, b.z, h);
+        const float4 cell = __ldg(&t.cells[flat_index(t, bn)]);
+        out4[i] = make_float4(cell.x * b.z, cell.y * b.z, cell.z * b.z, pdf_from_bins(t, v, a.z, b.z, h, bn.ih));
+    }
+};
+
+struct SampleAosOp {
+    static constexpr int kVec = 1;
+    const float4 *wi4, *u4;
+    float4 *wo4, *w4;
+
+    __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.image_full_floats; }
+
+    __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                            const int) const {
+        if (!in_range) return 0u;
+        const float4 a = __ldcs(wi4 + g), u = __ldcs(u4 + g);
+        const bool ok = a.z > 0.f;
+        const bool spec = u.x < t.spec_weight;
+        float x, y, z, sx, sy, sz;
+        cosine_hemisphere(u.y, u.z, x, y, z);
+        const int j = max(min((int)(a.z * (float)t.ni), t.ni - 1), 0);
+        const float* row = v.cdf + j * (t.nh + 1);
+        const int i = search_lane(row, t.nh, t.search_step, u.y);
+        spec_direction(v, row, i, a.x, a.y, a.z, u.y, u.z, sx, sy, sz);
+        x = spec ? sx : x; y = spec ? sy : y; z = spec ? sz : z;
+        const bool valid = ok && z > 0.f;
+        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, x, y, z);
+        unsigned unc;
+        int kc[3];
+        const Bins bn = compute_bins_fast(t, v, a.x, a.y, a.z, x, y, z, h, unc, kc);
+        const float4 cell = __ldg(&t.cells[flat_index(t, bn)]);
+        const float pq = pdf_from_bins(t, v, a.z, z, h, bn.ih);
+        const bool good = valid && pq > 0.f;
+        const float s = good ? __fdividef(z, pq) : 0.f;
+        __stcs(wo4 + g, make_float4(ok ? x : 0.f, ok ? y : 0.f, ok ? z : 0.f, good ? pq : 0.f));
+        __stcs(w4 + g, make_float4(cell.x * s, cell.y * s, cell.z * s, (ok && spec) ? 1.f : 0.f));
+        return (unsigned)((unc != 0u) & valid);
+    }
+    __device__ __forceinline__ void redo(const TableDev& t, const SmemView& v, const int64_t i) const {
+        const float4 a = wi4[i];
+        const float4 o = __ldcg(wo4 + i);
+        const float lobe = __ldcg(w4 + i).w;
+        const HalfDiff h = half_diff_setup(a.x, a.y, a.z, o.x, o.y, o.z);
+        const Bins bn = compute_bins(t, v, a.x, a.y, a.z, o.x, o.y, o.z, h);
+        const float4 cell = __ldg(&t.cells[flat_index(t, bn)]);
+        const float p = pdf_from_bins(t, v, a.z, o.z, h, bn.ih);
+        const bool good = p > 0.f;
+        const float s = good ? __fdividef(o.z, p) : 0.f;
+        wo4[i] = make_float4(o.x, o.y, o.z, good ? p : 0.f);
+        w4[i] = make_float4(cell.x * s, cell.y * s, cell.z * s, lobe);
+    }
+};
+
+}  // namespace merl
