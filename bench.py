@@ -307,7 +307,7 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": recorded_traffic(), "peak_source": peak_src,
-                         "algorithmic_bytes_per_query": BYTES_PER_QUERY, "kernel": "query_kernel<EVAL_PDF,4>",
+                         "algorithmic_bytes_per_query": BYTES_PER_QUERY, "kernel": "stream_kernel<QueryOp<EVAL_PDF,4>,3>",
                          "kernel_ms": kernel_ms},
             "extras": extras,
         }

@@ -21,6 +21,14 @@
 
 using namespace merl;
 
+// resident CTAs per SM the register allocation of the 4-wide sample / backward ops is capped for
+#ifndef MERL_SAMPLE_MINB
+#define MERL_SAMPLE_MINB 3
+#endif
+#ifndef MERL_BWD_MINB
+#define MERL_BWD_MINB 3
+#endif
+
 // ------------------------------------------------------------------------------------------
 // errors, counters
 // ------------------------------------------------------------------------------------------
@@ -582,7 +590,7 @@ static int run_sample(const merl_table* t, SampleIn in, int64_t n, SampleOut out
                      aligned(out.wg, 16) && aligned(out.wb, 16) && aligned(out.lobe, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_op<SampleOp<4, SEARCH>, 2>(t, SampleOp<4, SEARCH>{in, out}, fl, n / 4, s);
+        const int rc = launch_op<SampleOp<4, SEARCH>, MERL_SAMPLE_MINB>(t, SampleOp<4, SEARCH>{in, out}, fl, n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;
     }
@@ -625,7 +633,7 @@ static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* g
                      aligned(in.gg, 16) && aligned(in.gb, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_op<BackwardOp<4, AGG>, 2>(t, BackwardOp<4, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl,
+        const int rc = launch_op<BackwardOp<4, AGG>, MERL_BWD_MINB>(t, BackwardOp<4, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl,
                                                         n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;

@@ -13,7 +13,7 @@ timeout 300 python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
   --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline \
   > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:query_kernel -s 3 -c 1 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 3 -c 1 \
   -o gpurun_out/eval_pdf_full -f python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-extras \
   > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 tail -3 gpurun_out/pytest_gpu.log

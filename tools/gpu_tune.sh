@@ -1,4 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -15
-timeout 300 python tools/quick_perf.py 26 2>&1 | grep -E "^(eval|pdf|bins|sample|backward)" | tee gpurun_out/quick4.log
+for m in 3 4; do echo "== sample/backward MINB=$m"; MERL_B200_LIB=$PWD/build/libmerl_sb$m.so timeout 300 python tools/quick_perf.py 26 2>&1 | grep -E "^(sample_search0|backward)"; done | tee gpurun_out/quick5.log

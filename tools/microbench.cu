@@ -43,6 +43,29 @@ __global__ void stream_gather(const float4* __restrict__ table, const int4* __re
         __stcs(o3 + g, make_float4(u.x + v.x, u.y + v.y, u.z + v.z, u.w + v.w));
     }
 }
+// red16: idx stream (4 B) + one random red.global.add.v4.f32 into the 23.3 MB table
+// stream+red: the backward kernel's memory traffic without its math (36 B/query read + the RED)
+__device__ __forceinline__ void red4(float4* a, float x, float y, float z, float w) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__global__ void red16(float4* table, const int4* __restrict__ idx, long n4) {
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < n4; g += (long)gridDim.x * blockDim.x) {
+        int4 i = __ldcs(idx + g);
+        red4(table + i.x, 1.f, 2.f, 3.f, 1.f); red4(table + i.y, 1.f, 2.f, 3.f, 1.f);
+        red4(table + i.z, 1.f, 2.f, 3.f, 1.f); red4(table + i.w, 1.f, 2.f, 3.f, 1.f);
+    }
+}
+__global__ void stream_red(float4* table, const int4* __restrict__ idx, const float4* a, const float4* b,
+                           const float4* c, const float4* d, const float4* e, const float4* f, const float4* h,
+                           const float4* k, long n4) {
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < n4; g += (long)gridDim.x * blockDim.x) {
+        int4 i = __ldcs(idx + g);
+        float4 x = __ldcs(a + g), y = __ldcs(b + g), z = __ldcs(c + g), u = __ldcs(d + g), v = __ldcs(e + g),
+               w = __ldcs(f + g), p = __ldcs(h + g), q = __ldcs(k + g);
+        red4(table + i.x, x.x + u.x, y.x + v.x, z.x + w.x, p.x + q.x); red4(table + i.y, x.y + u.y, y.y + v.y, z.y + w.y, p.y + q.y);
+        red4(table + i.z, x.z + u.z, y.z + v.z, z.z + w.z, p.z + q.z); red4(table + i.w, x.w + u.w, y.w + v.w, z.w + w.w, p.w + q.w);
+    }
+}
 template <typename F> float timeit(F f, int iters = 10) {
     for (int i = 0; i < 3; ++i) f();
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -77,6 +100,10 @@ int main(int argc, char** argv) {
         printf("gather16 ldcg grid %4d: %7.3f ms  %7.1f Ggather/s\n", grid, ms, n / ms / 1e6);
         ms = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4); });
         printf("stream+gather grid %4d: %7.3f ms  %7.1f Gq/s  (%6.1f GB/s algorithmic at 40 B/q)\n", grid, ms, n / ms / 1e6, 40.0 * n / ms / 1e6);
+        ms = timeit([&] { red16<<<grid, 256>>>(table, idx, n4); });
+        printf("red16 v4      grid %4d: %7.3f ms  %7.1f Gred/s\n", grid, ms, n / ms / 1e6);
+        ms = timeit([&] { stream_red<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], in[5], out[0], out[1], n4); });
+        printf("stream+red    grid %4d: %7.3f ms  %7.1f Gq/s  (%6.1f GB/s algorithmic at 36 B/q)\n", grid, ms, n / ms / 1e6, 36.0 * n / ms / 1e6);
     }
     return 0;
 }
