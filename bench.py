@@ -278,12 +278,31 @@ def run_b200(args):
         ms_b, _ = timed(lambda: plug.backward(si, wo, g, grad_cells=grad), k, 3)
         extras["backward_gquery_s_no_allreduce"] = world * n / (ms_b / k * 1e-3) / 1e9
         if world > 1:
+            from mitsuba_customization_b200 import distributed as D
+            comm = D.Comm(rank, world, local)   # libmerl_b200's NCCL communicator (id shipped over torch.distributed)
+
             def bwd_ar():
                 plug.backward(si, wo, g, grad_cells=grad)
-                dist.all_reduce(grad)
+                comm.allreduce_sum_(grad)
             ms_ba, _ = timed(bwd_ar, k, 3)
             extras["backward_gquery_s_with_allreduce"] = world * n / (ms_ba / k * 1e-3) / 1e9
+            ms_ar, _ = timed(lambda: comm.allreduce_sum_(grad), k, 3)
+            extras["allreduce_ms"] = ms_ar / k
             extras["allreduce_bytes"] = grad.numel() * 4
+            # BASELINE config 4: 2^26 queries in TOTAL, sharded over the ranks (strong scaling), one allreduce
+            lo, hi = D.shard_bounds(1 << 26, world, rank)
+            m = min(hi - lo, n)
+            sw = bsdf.SurfaceInteraction3f(wi=wi[:, :m].contiguous())
+            swo, sg = wo[:, :m].contiguous(), g[:, :m].contiguous()
+
+            def bwd_strong():
+                plug.backward(sw, swo, sg, grad_cells=grad)
+                comm.allreduce_sum_(grad)
+            ms_bs, _ = timed(bwd_strong, k, 3)
+            extras["backward_2p26_total_ms_with_allreduce"] = ms_bs / k
+            extras["backward_2p26_total_gquery_s"] = (1 << 26) / (ms_bs / k * 1e-3) / 1e9
+            comm.close()
+            del sw, swo, sg
         del g, grad
 
     sampler.stop_flag = True

@@ -140,6 +140,21 @@ int merl_sample_host(const merl_table_t* t, const float* wix, const float* wiy, 
                      const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
                      float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe);
 
+/* ---- multi-GPU exchange step: table gradients and film buffers --------------
+ * The forward path shards by query batch with no collective.  The backward path keeps a private
+ * gradient table per GPU and sums them with ONE allreduce; a renderer sums (or gathers) film
+ * tiles the same way.  NCCL is bound at run time (dlopen of libnccl.so.2: the copy already loaded
+ * by the host process, e.g. PyTorch's, else the system one), so the library loads without it.
+ * One process per GPU: rank 0 calls merl_comm_unique_id, the host ships the 128 bytes to the
+ * other ranks by whatever it has (MPI, torch.distributed, a file), every rank calls
+ * merl_comm_create.  merl_allreduce_sum_f32 is in place, asynchronous on `stream`. */
+typedef struct merl_comm merl_comm_t;
+#define MERL_COMM_ID_BYTES 128
+int merl_comm_unique_id(void* id_out /* MERL_COMM_ID_BYTES */);
+int merl_comm_create(const void* id, int nranks, int rank, int device, merl_comm_t** out);
+int merl_comm_destroy(merl_comm_t* c);
+int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_stream_t stream);
+
 /* ---- diagnostics ------------------------------------------------------------------------ */
 const char* merl_last_error(void);
 int merl_abi_version(void);

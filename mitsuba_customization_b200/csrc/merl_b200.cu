@@ -4,6 +4,7 @@
 //                          stream_kernel<Op> with Op = QueryOp / SampleOp / BackwardOp /
 //                          EvalPdfAosOp / SampleAosOp (merl_kernels.cuh)
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -789,4 +790,90 @@ extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const 
     }
     for (int s = 0; s < HostPipe::kSlots; ++s) CUDA_TRY(cudaStreamSynchronize(p->stream[s]));
     return MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// multi-GPU exchange step: NCCL bound at run time (no link-time dependency)
+// ------------------------------------------------------------------------------------------
+namespace {
+struct NcclId { char bytes[MERL_COMM_ID_BYTES]; };   // ncclUniqueId (passed by value)
+struct NcclApi {
+    // the four entry points used, with NCCL's stable C signatures (nccl.h 2.x)
+    int (*GetUniqueId)(void* id) = nullptr;
+    int (*CommInitRank)(void** comm, int nranks, NcclId id, int rank) = nullptr;
+    int (*CommDestroy)(void* comm) = nullptr;
+    int (*AllReduce)(const void* send, void* recv, size_t count, int dtype, int op, void* comm, cudaStream_t s) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);   // the host's copy, if loaded
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return;
+        *(void**)&api.GetUniqueId = dlsym(h, "ncclGetUniqueId");
+        *(void**)&api.CommInitRank = dlsym(h, "ncclCommInitRank");
+        *(void**)&api.CommDestroy = dlsym(h, "ncclCommDestroy");
+        *(void**)&api.AllReduce = dlsym(h, "ncclAllReduce");
+        *(void**)&api.GetErrorString = dlsym(h, "ncclGetErrorString");
+        api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce;
+    });
+    return &api;
+}
+int nccl_fail(const char* what, int rc) {
+    NcclApi* a = nccl_api();
+    return fail(MERL_ERR_CUDA, "%s: NCCL error %d (%s)", what, rc, a->GetErrorString ? a->GetErrorString(rc) : "?");
+}
+}  // namespace
+
+struct merl_comm {
+    void* comm = nullptr;
+    int device = 0, nranks = 1, rank = 0;
+};
+
+extern "C" int merl_comm_unique_id(void* id_out) {
+    if (!id_out) return fail(MERL_ERR_ARG, "NULL argument");
+    NcclApi* a = nccl_api();
+    if (!a->ok) return fail(MERL_ERR_UNSUPPORTED, "libnccl.so.2 not found");
+    const int rc = a->GetUniqueId(id_out);
+    return rc ? nccl_fail("ncclGetUniqueId", rc) : MERL_OK;
+}
+
+extern "C" int merl_comm_create(const void* id, int nranks, int rank, int device, merl_comm_t** out) {
+    if (!id || !out || nranks < 1 || rank < 0 || rank >= nranks) return fail(MERL_ERR_ARG, "bad argument");
+    NcclApi* a = nccl_api();
+    if (!a->ok) return fail(MERL_ERR_UNSUPPORTED, "libnccl.so.2 not found");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(MERL_ERR_ARG, "device %d not in [0,%d)", device, ndev);
+    DeviceGuard g(device);
+    merl_comm* c = new merl_comm();
+    c->device = device; c->nranks = nranks; c->rank = rank;
+    NcclId idv;
+    memcpy(&idv, id, sizeof idv);
+    const int rc = a->CommInitRank(&c->comm, nranks, idv, rank);
+    if (rc) { delete c; return nccl_fail("ncclCommInitRank", rc); }
+    *out = c;
+    return MERL_OK;
+}
+
+extern "C" int merl_comm_destroy(merl_comm_t* c) {
+    if (!c) return MERL_OK;
+    NcclApi* a = nccl_api();
+    DeviceGuard g(c->device);
+    const int rc = (a->ok && c->comm) ? a->CommDestroy(c->comm) : 0;
+    delete c;
+    return rc ? nccl_fail("ncclCommDestroy", rc) : MERL_OK;
+}
+
+extern "C" int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_stream_t stream) {
+    if (!c || count < 0 || (count > 0 && !buf)) return fail(MERL_ERR_ARG, "bad argument");
+    if (count == 0) return MERL_OK;
+    NcclApi* a = nccl_api();
+    DeviceGuard g(c->device);
+    const int rc = a->AllReduce(buf, buf, (size_t)count, /*ncclFloat32*/ 7, /*ncclSum*/ 0, c->comm, (cudaStream_t)stream);
+    return rc ? nccl_fail("ncclAllReduce", rc) : MERL_OK;
 }

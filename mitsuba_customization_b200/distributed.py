@@ -1,0 +1,108 @@
+"""Multi-GPU host logic for the measured-BRDF path: one process per GPU.
+
+Forward eval / pdf / sample shard by query batch with the table replicated and NO collective.
+The backward keeps a private fp32 gradient table per GPU and sums them with one allreduce over
+NVLink (libmerl_b200's merl_allreduce_sum_f32, i.e. NCCL bound at run time); a renderer sums its
+film the same way.  torch.distributed is used only as the out-of-band channel that ships the
+128-byte NCCL id from rank 0 to the others (any backend: gloo on CPU, nccl on the GPU box).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _cabi
+from ._cabi import MerlError, check
+
+ID_BYTES = 128
+
+
+def shard_bounds(n: int, world: int, rank: int, align: int = 4) -> Tuple[int, int]:
+    """Contiguous shard [lo, hi) of n queries for `rank`; interior cuts are multiples of `align`
+    so every shard but the last keeps the 16-byte vector path.  Shards cover [0, n) exactly."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError(f"rank {rank} not in [0, {world})")
+    per = -(-n // world)              # ceil
+    per = -(-per // align) * align    # round up to the alignment
+    lo = min(rank * per, n)
+    hi = min(lo + per, n)
+    return lo, hi
+
+
+def table_owner(table_id: int, world: int) -> int:
+    """By-table sharding for multi-material scenes (BASELINE config 5): round-robin owner."""
+    return table_id % world
+
+
+def exchange_id(make_id, group=None) -> bytes:
+    """Rank 0 calls make_id() -> 128 bytes; everyone returns the same bytes.  Runs over any
+    initialised torch.distributed backend (tensors live on the backend's device)."""
+    import torch.distributed as dist
+
+    if not dist.is_initialized():
+        raise MerlError("torch.distributed is not initialised (needed to ship the communicator id)")
+    backend = dist.get_backend(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    buf = torch.zeros(ID_BYTES, dtype=torch.uint8)
+    if dist.get_rank(group) == 0:
+        raw = make_id()
+        if len(raw) != ID_BYTES:
+            raise MerlError(f"communicator id must be {ID_BYTES} bytes")
+        buf = torch.frombuffer(bytearray(raw), dtype=torch.uint8).clone()
+    buf = buf.to(dev)
+    dist.broadcast(buf, src=0, group=group)
+    return bytes(buf.cpu().numpy().tobytes())
+
+
+def _nccl_unique_id() -> bytes:
+    raw = (C.c_char * ID_BYTES)()
+    check(_cabi.lib().merl_comm_unique_id(C.cast(raw, C.c_void_p)))
+    return bytes(raw.raw)
+
+
+class Comm:
+    """libmerl_b200 communicator of this rank (wraps merl_comm_create / merl_allreduce_sum_f32)."""
+
+    def __init__(self, rank: int, world: int, device: int, id_bytes: Optional[bytes] = None):
+        self.rank, self.world, self.device = rank, world, device
+        if id_bytes is None:
+            id_bytes = exchange_id(_nccl_unique_id)
+        self._h = C.c_void_p()
+        buf = (C.c_char * ID_BYTES).from_buffer_copy(id_bytes)
+        check(_cabi.lib().merl_comm_create(C.cast(buf, C.c_void_p), world, rank, device, C.byref(self._h)))
+
+    def allreduce_sum_(self, t: torch.Tensor) -> torch.Tensor:
+        if t.dtype != torch.float32 or not t.is_cuda or not t.is_contiguous():
+            raise MerlError("allreduce_sum_ needs a contiguous float32 CUDA tensor")
+        stream = C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+        check(_cabi.lib().merl_allreduce_sum_f32(self._h, C.c_void_p(t.data_ptr()), t.numel(), stream))
+        return t
+
+    def close(self):
+        h, self._h = self._h, None
+        if h:
+            check(_cabi.lib().merl_comm_destroy(h))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def sharded_backward(plug, comm: Optional[Comm], si_wi: torch.Tensor, wo: torch.Tensor, grad_rgb: torch.Tensor,
+                     grad_cells: Optional[torch.Tensor] = None, warp_aggregate: bool = False,
+                     reduce: bool = True) -> torch.Tensor:
+    """This rank's shard of the queries -> private gradient table -> one allreduce.
+
+    si_wi / wo / grad_rgb are THIS RANK's shard, shape (3, n_local).  Returns the (ncell, 4)
+    gradient table, summed over ranks when `reduce` (the only collective on the path)."""
+    from .bsdf import SurfaceInteraction3f
+
+    g = plug.backward(SurfaceInteraction3f(wi=si_wi), wo, grad_rgb, grad_cells=grad_cells,
+                      warp_aggregate=warp_aggregate)
+    if reduce and comm is not None and comm.world > 1:
+        comm.allreduce_sum_(g)
+    return g
