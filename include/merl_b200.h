@@ -140,6 +140,42 @@ int merl_sample_host(const merl_table_t* t, const float* wix, const float* wiy, 
                      const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
                      float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe);
 
+/* ---- wavefront path tracer harness (BASELINE configs 2 and 5) ------------
+ * The callers either side of the BSDF stage, headless: spheres under a constant environment map,
+ * pinhole camera, path integrator with emitter sampling + BSDF sampling combined by the power
+ * heuristic, Philox4x32-10 random streams keyed by (pixel, sample, bounce).  Each bounce is a
+ * wavefront: trace -> (sort by material) -> BSDF stage (the eval_pdf / sample kernels above on
+ * float4 AoS buffers) -> shade.  oracle/render_oracle.c states the same algorithm on the CPU.
+ * film4: device float4[width*height], caller-zeroed; every finished path ADDS radiance/spp_total
+ * to its pixel (.w counts samples/spp_total), so ranks that render disjoint sample ranges
+ * [spp_begin, spp_end) of the same spp_total sum to the full image with one allreduce. */
+typedef struct merl_sphere {
+    float cx, cy, cz, radius;
+    int32_t material;          /* index into tables[] */
+    int32_t pad[3];
+} merl_sphere_t;
+
+typedef struct merl_render_params {
+    int32_t width, height;
+    int32_t spp_total;         /* normalisation                                         */
+    int32_t spp_begin, spp_end;/* sample indices this call renders for every pixel       */
+    int32_t max_depth;         /* surface interactions per path (>= 1)                   */
+    int32_t wavefront;         /* paths per pass; 0 = 1 << 21                            */
+    int32_t reserved;
+    uint64_t seed;
+    float cam_pos[3], cam_target[3], cam_up[3];
+    float fov_x_deg;
+    float env[3];              /* constant environment radiance (RGB)                    */
+} merl_render_params_t;
+
+typedef struct merl_render_stats {
+    int64_t paths, bsdf_queries, launches;
+} merl_render_stats_t;
+
+int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres_host, int nspheres,
+                const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out /* may be NULL */,
+                merl_stream_t stream);
+
 /* ---- multi-GPU exchange step: table gradients and film buffers --------------
  * The forward path shards by query batch with no collective.  The backward path keeps a private
  * gradient table per GPU and sums them with ONE allreduce; a renderer sums (or gathers) film

@@ -18,6 +18,7 @@
 
 #include "../../include/merl_b200.h"
 #include "merl_kernels.cuh"
+#include "merl_render.cuh"
 
 
 using namespace merl;
@@ -202,7 +203,6 @@ __global__ void dens_kernel(const float* __restrict__ cdf, const double* __restr
 // ------------------------------------------------------------------------------------------
 static constexpr int kThreads = 256;
 static constexpr size_t kMaxSmemBytes = 100 * 1024;   // per-table image (edges, densities, CDF rows)
-static constexpr size_t kMaxDynSmem = 227 * 1024;     // sm_100a opt-in limit per CTA
 
 template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
     // cached per (kernel instantiation, smem size)
@@ -212,7 +212,7 @@ template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
     const std::pair<const void*, size_t> key((const void*)kernel, smem);
     for (auto& e : cache)
         if (e.first == key) return e.second;
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kThreads, smem) != cudaSuccess || nb < 1) nb = 1;
     cache.push_back({key, nb});
@@ -876,4 +876,160 @@ extern "C" int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count,
     DeviceGuard g(c->device);
     const int rc = a->AllReduce(buf, buf, (size_t)count, /*ncclFloat32*/ 7, /*ncclSum*/ 0, c->comm, (cudaStream_t)stream);
     return rc ? nccl_fail("ncclAllReduce", rc) : MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// wavefront path tracer harness (merl_render.cuh): host driver
+// ------------------------------------------------------------------------------------------
+static void normalize3(float v[3]) {
+    const float l = sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    if (l > 0.f) { v[0] /= l; v[1] /= l; v[2] /= l; }
+}
+static void cross3(const float a[3], const float b[3], float o[3]) {
+    o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres, int nspheres,
+                           const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out,
+                           merl_stream_t stream_) {
+    if (!tables || !spheres || !p || !film4) return fail(MERL_ERR_ARG, "NULL argument");
+    if (ntables < 1 || ntables > 1024) return fail(MERL_ERR_ARG, "ntables must be in [1, 1024]");
+    if (nspheres < 1 || nspheres > kMaxSpheres) return fail(MERL_ERR_ARG, "nspheres must be in [1, %d]", kMaxSpheres);
+    if (p->width < 1 || p->height < 1 || p->max_depth < 1 || p->spp_total < 1 || p->spp_begin < 0 ||
+        p->spp_end < p->spp_begin || p->spp_end > p->spp_total)
+        return fail(MERL_ERR_ARG, "bad render parameters");
+    if (!aligned(film4, 16)) return fail(MERL_ERR_ARG, "film4 must be 16-byte aligned");
+    for (int k = 0; k < ntables; ++k) {
+        if (!tables[k]) return fail(MERL_ERR_ARG, "table %d is NULL", k);
+        if (tables[k]->device != tables[0]->device) return fail(MERL_ERR_ARG, "all tables must live on one device");
+    }
+    for (int k = 0; k < nspheres; ++k)
+        if (spheres[k].material < 0 || spheres[k].material >= ntables || !(spheres[k].radius > 0.f))
+            return fail(MERL_ERR_ARG, "sphere %d: bad material or radius", k);
+    const merl_table* t0 = tables[0];
+    DeviceGuard guard(t0->device);
+    cudaStream_t s = (cudaStream_t)stream_;
+
+    RenderDev R{};
+    R.width = p->width; R.height = p->height; R.spp_total = p->spp_total; R.spp_begin = p->spp_begin;
+    R.spp_end = p->spp_end; R.max_depth = p->max_depth; R.nspheres = nspheres; R.ntables = ntables;
+    R.k0 = (uint32_t)(p->seed & 0xffffffffu); R.k1 = (uint32_t)(p->seed >> 32);
+    for (int c = 0; c < 3; ++c) R.env[c] = p->env[c];
+    R.inv_spp = 1.0f / (float)p->spp_total;
+    {
+        float f[3] = {p->cam_target[0] - p->cam_pos[0], p->cam_target[1] - p->cam_pos[1], p->cam_target[2] - p->cam_pos[2]};
+        normalize3(f);
+        float up[3] = {p->cam_up[0], p->cam_up[1], p->cam_up[2]}, r[3], u[3];
+        cross3(f, up, r); normalize3(r); cross3(r, f, u);
+        const float th = tanf(0.5f * p->fov_x_deg * 3.14159265358979f / 180.f), asp = (float)p->height / (float)p->width;
+        R.cam = Camera{p->cam_pos[0], p->cam_pos[1], p->cam_pos[2], f[0], f[1], f[2], r[0] * th, r[1] * th, r[2] * th,
+                       u[0] * th * asp, u[1] * th * asp, u[2] * th * asp};
+    }
+    const int64_t npix = (int64_t)p->width * p->height;
+    const int64_t total = npix * (p->spp_end - p->spp_begin);
+    if (total == 0) { if (stats_out) memset(stats_out, 0, sizeof *stats_out); return MERL_OK; }
+    int64_t cap = p->wavefront > 0 ? p->wavefront : (1 << 21);
+    if (cap > total) cap = total;
+    cap = (cap + 255) & ~(int64_t)255;
+
+    // one stream-ordered workspace: path state, stage buffers, sort scratch, scene
+    const size_t nf = 19, ni = 4;
+    size_t bytes = cap * (nf * 4 + ni * 4) + cap * 16 * 9 + 256;
+    bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(3 * ntables + 2) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
+    char* ws = nullptr;
+    CUDA_TRY(cudaMallocAsync(&ws, bytes, s));
+    char* cur = ws;
+    auto take = [&](size_t b) { char* r = cur; cur += (b + 255) & ~(size_t)255; return r; };
+    float4* f4 = reinterpret_cast<float4*>(take(cap * 16 * 9));
+    StageBuf A{f4, f4 + cap, f4 + 2 * cap, f4 + 3 * cap, f4 + 4 * cap, f4 + 5 * cap};
+    StageBuf B{f4 + 6 * cap, f4 + 7 * cap, f4 + 8 * cap, A.fe4, A.wos4, A.w4};
+    float* fl = reinterpret_cast<float*>(take(cap * nf * 4));
+    int* in = reinterpret_cast<int*>(take(cap * ni * 4));
+    PathState P{fl, fl + cap, fl + 2 * cap, fl + 3 * cap, fl + 4 * cap, fl + 5 * cap, fl + 6 * cap, fl + 7 * cap,
+                fl + 8 * cap, fl + 9 * cap, fl + 10 * cap, fl + 11 * cap, fl + 12 * cap, fl + 13 * cap, fl + 14 * cap,
+                fl + 15 * cap, fl + 16 * cap, fl + 17 * cap, fl + 18 * cap, in, in + cap, in + 2 * cap, in + 3 * cap};
+    float4* d_sph = reinterpret_cast<float4*>(take((size_t)nspheres * 16));
+    int* d_smat = reinterpret_cast<int*>(take((size_t)nspheres * 4));
+    int* d_counts = reinterpret_cast<int*>(take((size_t)(3 * ntables + 2) * 4));
+    int *d_seg = d_counts + ntables, *d_cursor = d_seg + ntables + 1;
+    TableDev* d_tabs = reinterpret_cast<TableDev*>(take(sizeof(TableDev) * ntables));
+    unsigned long long* d_nq = reinterpret_cast<unsigned long long*>(take(8));
+
+    std::vector<float4> hs(nspheres);
+    std::vector<int> hm(nspheres);
+    for (int k = 0; k < nspheres; ++k) {
+        hs[k] = make_float4(spheres[k].cx, spheres[k].cy, spheres[k].cz, spheres[k].radius);
+        hm[k] = spheres[k].material;
+    }
+    std::vector<TableDev> ht(ntables);
+    int img_floats_eval = 0, img_floats_full = 0;
+    for (int k = 0; k < ntables; ++k) {
+        ht[k] = tables[k]->dev;
+        img_floats_eval = std::max(img_floats_eval, ht[k].image_eval_floats);
+        img_floats_full = std::max(img_floats_full, ht[k].image_full_floats);
+    }
+    int rc = MERL_OK;
+    int64_t launches = 0, op_launches = 0;   // raw <<<>>> launches here / launches through launch_op
+#define RT_TRY(x)                                                                                  \
+    do {                                                                                           \
+        cudaError_t e_ = (x);                                                                      \
+        if (e_ != cudaSuccess) {                                                                   \
+            rc = fail(MERL_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            goto done;                                                                             \
+        }                                                                                          \
+    } while (0)
+    {
+    RT_TRY(cudaMemcpyAsync(d_sph, hs.data(), sizeof(float4) * nspheres, cudaMemcpyHostToDevice, s));
+    RT_TRY(cudaMemcpyAsync(d_smat, hm.data(), sizeof(int) * nspheres, cudaMemcpyHostToDevice, s));
+    RT_TRY(cudaMemcpyAsync(d_tabs, ht.data(), sizeof(TableDev) * ntables, cudaMemcpyHostToDevice, s));
+    RT_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int) * ntables, s));
+    RT_TRY(cudaMemsetAsync(d_nq, 0, 8, s));
+    float4* film = reinterpret_cast<float4*>(film4);
+    for (int64_t first = 0; first < total; first += cap) {
+        const int np = (int)std::min<int64_t>(cap, total - first);
+        const int nb = (np + 255) / 256;
+        rt_raygen_kernel<<<nb, 256, 0, s>>>(R, P, first, np);
+        ++launches;
+        for (int depth = 0; depth <= p->max_depth; ++depth) {
+            rt_trace_kernel<<<nb, 256, 0, s>>>(R, P, A, d_sph, d_smat, np, depth, film, d_nq);
+            ++launches;
+            if (depth == p->max_depth) break;   // the last trace only collects escaped paths
+            if (ntables == 1) {
+                const EvalPdfAosOp e{A.wi4, A.woe4, A.fe4};
+                const SampleAosOp sm{A.wi4, A.u4, A.wos4, A.w4};
+                if ((rc = launch_op<EvalPdfAosOp, 4>(t0, e, t0->dev.image_eval_floats, np, s))) goto done;
+                if ((rc = launch_op<SampleAosOp, 3>(t0, sm, t0->dev.image_full_floats, np, s))) goto done;
+                op_launches += 2;
+                rt_shade_kernel<<<nb, 256, 0, s>>>(R, P, A, np, film);
+            } else {
+                rt_hist_kernel<<<std::min(nb, t0->num_sms * 4), 256, sizeof(int) * ntables, s>>>(P.mat, np, ntables, d_counts);
+                rt_scan_kernel<<<1, 32, 0, s>>>(d_counts, ntables, d_seg, d_cursor);
+                rt_scatter_kernel<<<nb, 256, 0, s>>>(P, A, B, np, d_cursor);
+                const EvalPdfAosOp e{B.wi4, B.woe4, B.fe4};
+                const SampleAosOp sm{B.wi4, B.u4, B.wos4, B.w4};
+                const int img_e = (int)(((size_t)img_floats_eval * 4 + 127) & ~(size_t)127);
+                const int img_f = (int)(((size_t)img_floats_full * 4 + 127) & ~(size_t)127);
+                const int grid_e = t0->num_sms * blocks_per_sm(stream_multi_kernel<EvalPdfAosOp, 4>, (size_t)img_e + kQueueBytes);
+                const int grid_f = t0->num_sms * blocks_per_sm(stream_multi_kernel<SampleAosOp, 3>, (size_t)img_f + kQueueBytes);
+                stream_multi_kernel<EvalPdfAosOp, 4><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, s>>>(d_tabs, ntables, d_seg, e, img_e);
+                stream_multi_kernel<SampleAosOp, 3><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, s>>>(d_tabs, ntables, d_seg, sm, img_f);
+                launches += 5;
+                rt_shade_kernel<<<nb, 256, 0, s>>>(R, P, B, np, film);
+            }
+            ++launches;
+        }
+        RT_TRY(cudaGetLastError());
+    }
+    g_launches.fetch_add(launches);
+    if (stats_out) {
+        unsigned long long nq = 0;
+        RT_TRY(cudaMemcpyAsync(&nq, d_nq, 8, cudaMemcpyDeviceToHost, s));
+        RT_TRY(cudaStreamSynchronize(s));
+        stats_out->paths = total; stats_out->bsdf_queries = (int64_t)nq; stats_out->launches = launches + op_launches;
+    }
+    }
+done:
+#undef RT_TRY
+    cudaFreeAsync(ws, s);
+    return rc;
 }

@@ -1,0 +1,328 @@
+// merl_render.cuh -- wavefront path tracer harness around the BSDF stage.
+//
+// The callers either side of the hot path, so that BASELINE configs 2 (one sphere, one table) and
+// 5 (many spheres, many tables) can be rendered and checked as images.  Headless: analytic
+// spheres, constant environment, pinhole camera, no graphics API.  Per bounce:
+//   rt_trace_kernel    intersect, terminate misses into the film, build the local frame, draw the
+//                      emitter direction + shadow ray, write the BSDF-stage inputs (float4 AoS)
+//   rt_sort_*          multi-material scenes only: counting sort of the live paths by material so
+//                      that each table's queries are one contiguous segment
+//   BSDF stage         EvalPdfAosOp + SampleAosOp (the kernels of the C ABI's *_aos entry points),
+//                      one launch pair per bounce; segmented over tables when there are several
+//   rt_shade_kernel    MIS-weighted emitter contribution, throughput update, next ray
+// The CPU oracle restates the same algorithm for the tests.  Included once, by merl_b200.cu.
+#pragma once
+#include "merl_kernels.cuh"
+
+namespace merl {
+
+// ---- Philox4x32-10: counter (pixel, sample, dimension block, 0), key = seed ------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+struct Camera {
+    float px, py, pz;     // position
+    float fx, fy, fz;     // forward
+    float rx, ry, rz;     // right * tan(fov_x/2)
+    float ux, uy, uz;     // up * tan(fov_x/2) * height/width
+};
+
+struct RenderDev {
+    int width, height, spp_total, spp_begin, spp_end, max_depth;
+    int nspheres, ntables;
+    uint32_t k0, k1;
+    float env[3];
+    float inv_spp;
+    Camera cam;
+};
+
+// Path state of one wavefront pass, SoA over `cap` paths (device workspace).
+struct PathState {
+    float *ox, *oy, *oz, *dx, *dy, *dz;       // current ray
+    float *tr, *tg, *tb;                      // throughput
+    float *lr, *lg, *lb;                      // accumulated radiance
+    float* prev_pdf;                          // solid-angle pdf of the direction that produced the ray (0 = camera)
+    float *nx, *ny, *nz;                      // shading normal at the current hit
+    float *hx, *hy, *hz;                      // hit point
+    int* pixel;                               // -1 = dead
+    int* sample;
+    int* slot;                                // position of this path's query in the (sorted) stage buffers
+    int* mat;                                 // material at the current hit, -1 when the path has no query this bounce
+};
+
+constexpr int kMaxSpheres = 256;
+constexpr float kRayEps = 1e-4f;
+
+__device__ __forceinline__ void film_add(float4* film, int pixel, float r, float g, float b, float w) {
+    red_add_v4(film + pixel, r, g, b, w);
+}
+
+// nearest hit of (o, d) with the spheres in shared memory; returns sphere index or -1
+__device__ __forceinline__ int intersect_spheres(const float4* sph, int n, float ox, float oy, float oz, float dx,
+                                                 float dy, float dz, float& t_hit) {
+    int best = -1;
+    float tb = 3.0e38f;
+    for (int s = 0; s < n; ++s) {
+        const float4 c = sph[s];
+        const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
+        const float b = lx * dx + ly * dy + lz * dz;
+        const float cc = lx * lx + ly * ly + lz * lz - c.w * c.w;
+        const float disc = b * b - cc;
+        if (disc < 0.f) continue;
+        const float sq = sqrtf(disc);
+        float t = -b - sq;
+        if (t < kRayEps) t = -b + sq;
+        if (t >= kRayEps && t < tb) { tb = t; best = s; }
+    }
+    t_hit = tb;
+    return best;
+}
+__device__ __forceinline__ bool occluded(const float4* sph, int n, float ox, float oy, float oz, float dx, float dy,
+                                         float dz) {
+    for (int s = 0; s < n; ++s) {
+        const float4 c = sph[s];
+        const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
+        const float b = lx * dx + ly * dy + lz * dz;
+        const float cc = lx * lx + ly * ly + lz * lz - c.w * c.w;
+        const float disc = b * b - cc;
+        if (disc < 0.f) continue;
+        const float sq = sqrtf(disc);
+        if (-b - sq >= kRayEps || -b + sq >= kRayEps) return true;
+    }
+    return false;
+}
+
+// Duff et al. orthonormal basis (Mitsuba 3's coordinate_system)
+__device__ __forceinline__ void frame_from_normal(float nx, float ny, float nz, float s[3], float t[3]) {
+    const float sign = copysignf(1.f, nz);
+    const float a = -1.f / (sign + nz);
+    const float b = nx * ny * a;
+    s[0] = 1.f + sign * nx * nx * a; s[1] = sign * b; s[2] = -sign * nx;
+    t[0] = b; t[1] = sign + ny * ny * a; t[2] = -ny;
+}
+__device__ __forceinline__ float power_heuristic(float a, float b) {
+    const float a2 = a * a, b2 = b * b;
+    return a2 > 0.f ? a2 / (a2 + b2) : 0.f;
+}
+
+// ---- ray generation: path i of the pass <-> global sample (first + i) ----------------------------
+__global__ void rt_raygen_kernel(const RenderDev R, const PathState P, const int64_t first, const int npaths) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npaths) return;
+    const int64_t gid = first + i;
+    const int npix = R.width * R.height;
+    const int pixel = (int)(gid % npix), s = R.spp_begin + (int)(gid / npix);
+    uint32_t rnd[4];
+    philox4x32_10((uint32_t)pixel, (uint32_t)s, 0u, 0u, R.k0, R.k1, rnd);
+    const int x = pixel % R.width, y = pixel / R.width;
+    const float sx = ((float)x + u01(rnd[0])) / (float)R.width * 2.f - 1.f;
+    const float sy = 1.f - ((float)y + u01(rnd[1])) / (float)R.height * 2.f;
+    const Camera& c = R.cam;
+    float dx = c.fx + sx * c.rx + sy * c.ux, dy = c.fy + sx * c.ry + sy * c.uy, dz = c.fz + sx * c.rz + sy * c.uz;
+    const float inv = rsqrtf(dx * dx + dy * dy + dz * dz);
+    P.ox[i] = c.px; P.oy[i] = c.py; P.oz[i] = c.pz;
+    P.dx[i] = dx * inv; P.dy[i] = dy * inv; P.dz[i] = dz * inv;
+    P.tr[i] = 1.f; P.tg[i] = 1.f; P.tb[i] = 1.f;
+    P.lr[i] = 0.f; P.lg[i] = 0.f; P.lb[i] = 0.f;
+    P.prev_pdf[i] = 0.f;
+    P.pixel[i] = pixel; P.sample[i] = s;
+    P.mat[i] = -1; P.slot[i] = i;
+}
+
+// BSDF-stage buffers of one pass (float4 AoS over `cap` slots)
+struct StageBuf {
+    float4 *wi4, *woe4, *u4;        // inputs: wi (w = material), emitter direction (z < 0: none), random numbers
+    float4 *fe4, *wos4, *w4;        // outputs: (f cos, pdf_b) at woe; (wo, pdf) sampled; (weight, lobe)
+};
+
+// ---- trace: intersect, terminate misses, prepare the BSDF-stage inputs ---------------------------
+__global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const PathState P, const StageBuf S,
+                                                       const float4* __restrict__ spheres,
+                                                       const int* __restrict__ sphere_mat, const int npaths,
+                                                       const int depth, float4* __restrict__ film,
+                                                       unsigned long long* __restrict__ nquery) {
+    __shared__ float4 sph[kMaxSpheres];
+    __shared__ int smat[kMaxSpheres];
+    for (int s = threadIdx.x; s < R.nspheres; s += blockDim.x) { sph[s] = spheres[s]; smat[s] = sphere_mat[s]; }
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npaths) return;
+    const int pixel = P.pixel[i];
+    const float4 dead = make_float4(0.f, 0.f, -1.f, 0.f);
+    if (pixel < 0) { P.mat[i] = -1; S.wi4[i] = dead; S.woe4[i] = dead; return; }
+    const float ox = P.ox[i], oy = P.oy[i], oz = P.oz[i], dx = P.dx[i], dy = P.dy[i], dz = P.dz[i];
+    float t;
+    const int hit = intersect_spheres(sph, R.nspheres, ox, oy, oz, dx, dy, dz, t);
+    bool finish = false;
+    float lr = P.lr[i], lg = P.lg[i], lb = P.lb[i];
+    if (hit < 0) {
+        // escaped: environment radiance, MIS against the emitter sample of the previous bounce
+        const float w = depth == 0 ? 1.f : power_heuristic(P.prev_pdf[i], 0.0795774715f);
+        lr = fmaf(P.tr[i] * R.env[0], w, lr); lg = fmaf(P.tg[i] * R.env[1], w, lg); lb = fmaf(P.tb[i] * R.env[2], w, lb);
+        finish = true;
+    } else if (depth >= R.max_depth) {
+        finish = true;   // interaction budget used up
+    }
+    float wix = 0.f, wiy = 0.f, wiz = -1.f, nx = 0.f, ny = 0.f, nz = 1.f, hx = 0.f, hy = 0.f, hz = 0.f;
+    float s[3], tt[3];
+    if (!finish) {
+        const float4 c = sph[hit];
+        hx = fmaf(t, dx, ox); hy = fmaf(t, dy, oy); hz = fmaf(t, dz, oz);
+        const float ir = 1.f / c.w;
+        nx = (hx - c.x) * ir; ny = (hy - c.y) * ir; nz = (hz - c.z) * ir;
+        const float inv = rsqrtf(nx * nx + ny * ny + nz * nz);
+        nx *= inv; ny *= inv; nz *= inv;
+        frame_from_normal(nx, ny, nz, s, tt);
+        wix = -(dx * s[0] + dy * s[1] + dz * s[2]);
+        wiy = -(dx * tt[0] + dy * tt[1] + dz * tt[2]);
+        wiz = -(dx * nx + dy * ny + dz * nz);
+        if (!(wiz > 0.f)) finish = true;   // grazing / inside hit: nothing to shade
+    }
+    if (finish) {
+        film_add(film, pixel, lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
+        P.pixel[i] = -1; P.mat[i] = -1; S.wi4[i] = dead; S.woe4[i] = dead;
+        return;
+    }
+    uint32_t re[4], rb[4];
+    philox4x32_10((uint32_t)pixel, (uint32_t)P.sample[i], (uint32_t)(2 * depth + 1), 0u, R.k0, R.k1, re);
+    philox4x32_10((uint32_t)pixel, (uint32_t)P.sample[i], (uint32_t)(2 * depth + 2), 0u, R.k0, R.k1, rb);
+    // emitter sampling: uniform direction on the sphere (constant environment), pdf 1/(4 pi)
+    const float ez = 1.f - 2.f * u01(re[0]);
+    const float er = sqrtf(fmaxf(0.f, 1.f - ez * ez));
+    float es, ec;
+    sincospif(2.f * u01(re[1]), &es, &ec);
+    const float ex = er * ec, ey = er * es;
+    float4 woe = dead;
+    const float lz = ex * nx + ey * ny + ez * nz;
+    if (lz > 0.f && !occluded(sph, R.nspheres, fmaf(kRayEps, nx, hx), fmaf(kRayEps, ny, hy), fmaf(kRayEps, nz, hz), ex, ey, ez))
+        woe = make_float4(ex * s[0] + ey * s[1] + ez * s[2], ex * tt[0] + ey * tt[1] + ez * tt[2], lz, 0.f);
+    const int m = smat[hit];
+    {   // one counter update per warp: live BSDF queries of this bounce
+        const unsigned live = __activemask();
+        if ((threadIdx.x & 31) == __ffs(live) - 1) atomicAdd(nquery, (unsigned long long)__popc(live));
+    }
+    P.lr[i] = lr; P.lg[i] = lg; P.lb[i] = lb;
+    P.nx[i] = nx; P.ny[i] = ny; P.nz[i] = nz; P.hx[i] = hx; P.hy[i] = hy; P.hz[i] = hz;
+    P.mat[i] = m; P.slot[i] = i;
+    S.wi4[i] = make_float4(wix, wiy, wiz, (float)m);
+    S.woe4[i] = woe;
+    S.u4[i] = make_float4(u01(rb[0]), u01(rb[1]), u01(rb[2]), 0.f);
+}
+
+// ---- counting sort of the live queries by material (multi-material scenes) -----------------------
+__global__ void rt_hist_kernel(const int* __restrict__ mat, const int npaths, const int ntables, int* counts) {
+    extern __shared__ int h[];
+    for (int k = threadIdx.x; k < ntables; k += blockDim.x) h[k] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npaths; i += gridDim.x * blockDim.x) {
+        const int m = mat[i];
+        if (m >= 0) atomicAdd(&h[m], 1);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < ntables; k += blockDim.x)
+        if (h[k]) atomicAdd(&counts[k], h[k]);
+}
+// seg_off[0..ntables] = exclusive scan of counts; cursor = seg_off; counts are cleared for the next bounce
+__global__ void rt_scan_kernel(int* counts, const int ntables, int* seg_off, int* cursor) {
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int k = 0; k < ntables; ++k) { seg_off[k] = run; cursor[k] = run; run += counts[k]; counts[k] = 0; }
+        seg_off[ntables] = run;
+    }
+}
+__global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B, const int npaths, int* cursor) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int m = i < npaths ? P.mat[i] : -1;
+    // one atomic per (warp, material): neighbouring pixels mostly share a material
+    const unsigned peers = __match_any_sync(0xffffffffu, m);
+    int base = 0;
+    const int leader = __ffs(peers) - 1;
+    if (m >= 0 && lane == leader) base = atomicAdd(&cursor[m], __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (m < 0) return;
+    const int slot = base + __popc(peers & ((1u << lane) - 1u));
+    P.slot[i] = slot;
+    B.wi4[slot] = A.wi4[i]; B.woe4[slot] = A.woe4[i]; B.u4[slot] = A.u4[i];
+}
+
+// ---- shade: consume the BSDF-stage outputs, continue or finish the path -------------------------------
+__global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const PathState P, const StageBuf S,
+                                                       const int npaths, float4* __restrict__ film) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npaths || P.mat[i] < 0) return;
+    const int slot = P.slot[i];
+    const float4 fe = S.fe4[slot], ws = S.wos4[slot], w = S.w4[slot];
+    float tr = P.tr[i], tg = P.tg[i], tb = P.tb[i];
+    const float mis = power_heuristic(0.0795774715f, fe.w) * 12.5663706f;   // weight / pdf_e
+    const float lr = fmaf(tr * fe.x * R.env[0], mis, P.lr[i]), lg = fmaf(tg * fe.y * R.env[1], mis, P.lg[i]),
+                lb = fmaf(tb * fe.z * R.env[2], mis, P.lb[i]);
+    tr *= w.x; tg *= w.y; tb *= w.z;
+    if (!(ws.w > 0.f) || !(tr + tg + tb > 0.f)) {
+        film_add(film, P.pixel[i], lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
+        P.pixel[i] = -1; P.mat[i] = -1;
+        return;
+    }
+    const float nx = P.nx[i], ny = P.ny[i], nz = P.nz[i];
+    float s[3], tt[3];
+    frame_from_normal(nx, ny, nz, s, tt);
+    P.dx[i] = ws.x * s[0] + ws.y * tt[0] + ws.z * nx;
+    P.dy[i] = ws.x * s[1] + ws.y * tt[1] + ws.z * ny;
+    P.dz[i] = ws.x * s[2] + ws.y * tt[2] + ws.z * nz;
+    P.ox[i] = fmaf(kRayEps, nx, P.hx[i]); P.oy[i] = fmaf(kRayEps, ny, P.hy[i]); P.oz[i] = fmaf(kRayEps, nz, P.hz[i]);
+    P.tr[i] = tr; P.tg[i] = tg; P.tb[i] = tb;
+    P.lr[i] = lr; P.lg[i] = lg; P.lb[i] = lb;
+    P.prev_pdf[i] = ws.w;
+}
+
+// ---- BSDF stage over several tables: the sorted query range is cut into one contiguous block per
+// CTA; a CTA walks the table segments its block overlaps, restaging the table image per segment ---
+template <typename Op, int MINB>
+__global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_multi_kernel(const TableDev* __restrict__ tabs,
+                                                                            const int ntables,
+                                                                            const int* __restrict__ seg_off,
+                                                                            const Op op, const int image_bytes) {
+    extern __shared__ float4 smem4[];
+    __shared__ TableDev t;
+    float* smem = reinterpret_cast<float*>(smem4);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const WarpQueue wq = warp_queue(reinterpret_cast<char*>(smem4) + image_bytes, warp);
+    if (lane == 0) *wq.count = 0;
+    const int total = seg_off[ntables];
+    int per = (total + gridDim.x - 1) / gridDim.x;
+    per = (per + 31) & ~31;
+    const int lo = min((int)blockIdx.x * per, total), hi = min(lo + per, total);
+    if (lo >= hi) return;
+    int m = 0;   // first segment that ends after lo
+    { int a = 0, b = ntables; while (a < b) { const int c = (a + b) >> 1; if (seg_off[c + 1] > lo) b = c; else a = c + 1; } m = a; }
+    for (; m < ntables && seg_off[m] < hi; ++m) {
+        const int a = max(lo, seg_off[m]), b = min(hi, seg_off[m + 1]);
+        if (a >= b) continue;
+        __syncthreads();   // previous segment fully processed (queues flushed) before the image changes
+        if (threadIdx.x == 0) t = tabs[m];
+        __syncthreads();
+        stage_image(t, smem, op.image_floats(t));
+        const SmemView v = make_view(t, smem);
+        for (int g0 = a + warp * 32; g0 < b; g0 += kWarpsPerCta * 32) {
+            const int64_t g = g0 + lane;
+            const unsigned q = op.hot(t, v, g, g < b, lane);
+            if (q) wq.items[atomicAdd(wq.count, 1)] = g;
+            __syncwarp();
+            if (*reinterpret_cast<volatile int*>(wq.count) > kQueueCap - 32) flush_queue(op, t, v, wq, lane);
+        }
+        flush_queue(op, t, v, wq, lane);
+    }
+}
+
+}  // namespace merl
