@@ -935,7 +935,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     // one stream-ordered workspace: path state, stage buffers, sort scratch, scene
     const size_t nf = 19, ni = 4;
     size_t bytes = cap * (nf * 4 + ni * 4) + cap * 16 * 9 + 256;
-    bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(3 * ntables + 2) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
+    bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(4 * ntables + 4) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
     char* ws = nullptr;
     CUDA_TRY(cudaMallocAsync(&ws, bytes, s));
     char* cur = ws;
@@ -950,8 +950,8 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
                 fl + 15 * cap, fl + 16 * cap, fl + 17 * cap, fl + 18 * cap, in, in + cap, in + 2 * cap, in + 3 * cap};
     float4* d_sph = reinterpret_cast<float4*>(take((size_t)nspheres * 16));
     int* d_smat = reinterpret_cast<int*>(take((size_t)nspheres * 4));
-    int* d_counts = reinterpret_cast<int*>(take((size_t)(3 * ntables + 2) * 4));
-    int *d_seg = d_counts + ntables, *d_cursor = d_seg + ntables + 1;
+    int* d_counts = reinterpret_cast<int*>(take((size_t)(4 * ntables + 4) * 4));
+    int *d_seg = d_counts + ntables, *d_cursor = d_seg + ntables + 1, *d_items = d_cursor + ntables;
     TableDev* d_tabs = reinterpret_cast<TableDev*>(take(sizeof(TableDev) * ntables));
     unsigned long long* d_nq = reinterpret_cast<unsigned long long*>(take(8));
 
@@ -968,8 +968,12 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         img_floats_eval = std::max(img_floats_eval, ht[k].image_eval_floats);
         img_floats_full = std::max(img_floats_full, ht[k].image_full_floats);
     }
+    const int img_e = (int)(((size_t)img_floats_eval * 4 + 127) & ~(size_t)127);
+    const int img_f = (int)(((size_t)img_floats_full * 4 + 127) & ~(size_t)127);
+    const int grid_e = t0->num_sms * blocks_per_sm(stream_multi_kernel<EvalPdfAosOp, 4>, (size_t)img_e + kQueueBytes);
+    const int grid_f = t0->num_sms * blocks_per_sm(stream_multi_kernel<SampleAosOp, 3>, (size_t)img_f + kQueueBytes);
     int rc = MERL_OK;
-    int64_t launches = 0, op_launches = 0;   // raw <<<>>> launches here / launches through launch_op
+    int64_t launches = 0;
 #define RT_TRY(x)                                                                                  \
     do {                                                                                           \
         cudaError_t e_ = (x);                                                                      \
@@ -994,29 +998,17 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
             rt_trace_kernel<<<nb, 256, 0, s>>>(R, P, A, d_sph, d_smat, np, depth, film, d_nq);
             ++launches;
             if (depth == p->max_depth) break;   // the last trace only collects escaped paths
-            if (ntables == 1) {
-                const EvalPdfAosOp e{A.wi4, A.woe4, A.fe4};
-                const SampleAosOp sm{A.wi4, A.u4, A.wos4, A.w4};
-                if ((rc = launch_op<EvalPdfAosOp, 4>(t0, e, t0->dev.image_eval_floats, np, s))) goto done;
-                if ((rc = launch_op<SampleAosOp, 3>(t0, sm, t0->dev.image_full_floats, np, s))) goto done;
-                op_launches += 2;
-                rt_shade_kernel<<<nb, 256, 0, s>>>(R, P, A, np, film);
-            } else {
-                rt_hist_kernel<<<std::min(nb, t0->num_sms * 4), 256, sizeof(int) * ntables, s>>>(P.mat, np, ntables, d_counts);
-                rt_scan_kernel<<<1, 32, 0, s>>>(d_counts, ntables, d_seg, d_cursor);
-                rt_scatter_kernel<<<nb, 256, 0, s>>>(P, A, B, np, d_cursor);
-                const EvalPdfAosOp e{B.wi4, B.woe4, B.fe4};
-                const SampleAosOp sm{B.wi4, B.u4, B.wos4, B.w4};
-                const int img_e = (int)(((size_t)img_floats_eval * 4 + 127) & ~(size_t)127);
-                const int img_f = (int)(((size_t)img_floats_full * 4 + 127) & ~(size_t)127);
-                const int grid_e = t0->num_sms * blocks_per_sm(stream_multi_kernel<EvalPdfAosOp, 4>, (size_t)img_e + kQueueBytes);
-                const int grid_f = t0->num_sms * blocks_per_sm(stream_multi_kernel<SampleAosOp, 3>, (size_t)img_f + kQueueBytes);
-                stream_multi_kernel<EvalPdfAosOp, 4><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, s>>>(d_tabs, ntables, d_seg, e, img_e);
-                stream_multi_kernel<SampleAosOp, 3><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, s>>>(d_tabs, ntables, d_seg, sm, img_f);
-                launches += 5;
-                rt_shade_kernel<<<nb, 256, 0, s>>>(R, P, B, np, film);
-            }
-            ++launches;
+            // live queries -> contiguous, material-sorted segments (with one table this is plain
+            // stream compaction: the BSDF stage then touches live queries only)
+            rt_hist_kernel<<<std::min(nb, t0->num_sms * 4), 256, sizeof(int) * ntables, s>>>(P.mat, np, ntables, d_counts);
+            rt_scan_kernel<<<1, 1024, 0, s>>>(d_counts, ntables, d_seg, d_cursor, d_items, 4 * std::min(grid_e, grid_f));
+            rt_scatter_kernel<<<nb, 256, 0, s>>>(P, A, B, np, d_cursor);
+            stream_multi_kernel<EvalPdfAosOp, 4><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, s>>>(
+                d_tabs, ntables, d_seg, d_items, EvalPdfAosOp{B.wi4, B.woe4, B.fe4}, img_e);
+            stream_multi_kernel<SampleAosOp, 3><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, s>>>(
+                d_tabs, ntables, d_seg, d_items, SampleAosOp{B.wi4, B.u4, B.wos4, B.w4}, img_f);
+            rt_shade_kernel<<<nb, 256, 0, s>>>(R, P, B, np, film);
+            launches += 6;
         }
         RT_TRY(cudaGetLastError());
     }
@@ -1025,7 +1017,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         unsigned long long nq = 0;
         RT_TRY(cudaMemcpyAsync(&nq, d_nq, 8, cudaMemcpyDeviceToHost, s));
         RT_TRY(cudaStreamSynchronize(s));
-        stats_out->paths = total; stats_out->bsdf_queries = (int64_t)nq; stats_out->launches = launches + op_launches;
+        stats_out->paths = total; stats_out->bsdf_queries = (int64_t)nq; stats_out->launches = launches;
     }
     }
 done:

@@ -77,8 +77,10 @@ __device__ __forceinline__ int intersect_spheres(const float4* sph, int n, float
         const float4 c = sph[s];
         const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
         const float b = lx * dx + ly * dy + lz * dz;
-        const float cc = lx * lx + ly * ly + lz * lz - c.w * c.w;
-        const float disc = b * b - cc;
+        // discriminant from the rejection of l on d (|l - b d|^2), not b^2 - (|l|^2 - r^2): the latter
+        // cancels catastrophically in fp32 when the origin is many radii away (Ray Tracing Gems ch. 7)
+        const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
+        const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
         if (disc < 0.f) continue;
         const float sq = sqrtf(disc);
         float t = -b - sq;
@@ -94,8 +96,8 @@ __device__ __forceinline__ bool occluded(const float4* sph, int n, float ox, flo
         const float4 c = sph[s];
         const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
         const float b = lx * dx + ly * dy + lz * dz;
-        const float cc = lx * lx + ly * ly + lz * lz - c.w * c.w;
-        const float disc = b * b - cc;
+        const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
+        const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
         if (disc < 0.f) continue;
         const float sq = sqrtf(disc);
         if (-b - sq >= kRayEps || -b + sq >= kRayEps) return true;
@@ -233,13 +235,45 @@ __global__ void rt_hist_kernel(const int* __restrict__ mat, const int npaths, co
     for (int k = threadIdx.x; k < ntables; k += blockDim.x)
         if (h[k]) atomicAdd(&counts[k], h[k]);
 }
-// seg_off[0..ntables] = exclusive scan of counts; cursor = seg_off; counts are cleared for the next bounce
-__global__ void rt_scan_kernel(int* counts, const int ntables, int* seg_off, int* cursor) {
-    if (threadIdx.x == 0) {
-        int run = 0;
-        for (int k = 0; k < ntables; ++k) { seg_off[k] = run; cursor[k] = run; run += counts[k]; counts[k] = 0; }
-        seg_off[ntables] = run;
+// One CTA of 1024 threads (ntables <= 1024), Hillis-Steele scans in shared memory:
+//   seg_off[0..ntables]   exclusive scan of counts (cursor = copy; counts cleared for the next bounce)
+//   item_off[0..ntables]  exclusive scan of ceil(count / chunk): the BSDF stage's work items, each at
+//                         most `chunk` queries of ONE table; item_off[ntables + 1] = chunk.
+// chunk adapts to the wavefront: ~target_items items in total, so fat wavefronts give every CTA a
+// few items and thin ones (late bounces) still spread over many CTAs instead of one CTA walking
+// many tables.
+__global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int ntables, int* seg_off, int* cursor,
+                                                       int* item_off, const int target_items) {
+    __shared__ int sc[1024];
+    __shared__ int chunk_s;
+    const int k = threadIdx.x;
+    const int c = k < ntables ? counts[k] : 0;
+    auto scan = [&](int v) {
+        sc[k] = v;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            const int add = k >= o ? sc[k - o] : 0;
+            __syncthreads();
+            sc[k] += add;
+            __syncthreads();
+        }
+        return sc[k];
+    };
+    const int inc = scan(c);
+    if (k < ntables) { seg_off[k] = inc - c; cursor[k] = inc - c; counts[k] = 0; }
+    if (k == 1023) {
+        int ch = (sc[1023] + target_items - 1) / max(target_items, 1);
+        ch = (ch + 31) & ~31;
+        chunk_s = min(max(ch, 128), 8192);
     }
+    if (k == ntables - 1) seg_off[ntables] = inc;
+    __syncthreads();
+    const int chunk = chunk_s;
+    const int items = (c + chunk - 1) / chunk;
+    __syncthreads();
+    const int iinc = scan(items);
+    if (k < ntables) item_off[k] = iinc - items;
+    if (k == ntables - 1) { item_off[ntables] = iinc; item_off[ntables + 1] = chunk; }
 }
 __global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B, const int npaths, int* cursor) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -286,12 +320,13 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
     P.prev_pdf[i] = ws.w;
 }
 
-// ---- BSDF stage over several tables: the sorted query range is cut into one contiguous block per
-// CTA; a CTA walks the table segments its block overlaps, restaging the table image per segment ---
+// ---- BSDF stage over several tables: work items (one table, <= chunk queries) are dealt to the CTAs
+// in contiguous blocks, so a CTA restages the table image only when its next item is another table --
 template <typename Op, int MINB>
 __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_multi_kernel(const TableDev* __restrict__ tabs,
                                                                             const int ntables,
                                                                             const int* __restrict__ seg_off,
+                                                                            const int* __restrict__ item_off,
                                                                             const Op op, const int image_bytes) {
     extern __shared__ float4 smem4[];
     __shared__ TableDev t;
@@ -299,20 +334,23 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_multi_kernel(cons
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const WarpQueue wq = warp_queue(reinterpret_cast<char*>(smem4) + image_bytes, warp);
     if (lane == 0) *wq.count = 0;
-    const int total = seg_off[ntables];
-    int per = (total + gridDim.x - 1) / gridDim.x;
-    per = (per + 31) & ~31;
-    const int lo = min((int)blockIdx.x * per, total), hi = min(lo + per, total);
-    if (lo >= hi) return;
-    int m = 0;   // first segment that ends after lo
-    { int a = 0, b = ntables; while (a < b) { const int c = (a + b) >> 1; if (seg_off[c + 1] > lo) b = c; else a = c + 1; } m = a; }
-    for (; m < ntables && seg_off[m] < hi; ++m) {
-        const int a = max(lo, seg_off[m]), b = min(hi, seg_off[m + 1]);
-        if (a >= b) continue;
-        __syncthreads();   // previous segment fully processed (queues flushed) before the image changes
-        if (threadIdx.x == 0) t = tabs[m];
-        __syncthreads();
-        stage_image(t, smem, op.image_floats(t));
+    const int nitems = item_off[ntables], chunk = item_off[ntables + 1];
+    const int ipc = (nitems + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int i0 = min((int)blockIdx.x * ipc, nitems), i1 = min(i0 + ipc, nitems);
+    if (i0 >= i1) return;
+    int m = 0;   // table of item i0: last m with item_off[m] <= i0
+    { int a = 0, b = ntables; while (b - a > 1) { const int c = (a + b) >> 1; if (item_off[c] <= i0) a = c; else b = c; } m = a; }
+    int staged = -1;
+    for (int item = i0; item < i1; ++item) {
+        while (item_off[m + 1] <= item) ++m;
+        const int a = seg_off[m] + (item - item_off[m]) * chunk, b = min(a + chunk, seg_off[m + 1]);
+        if (m != staged) {
+            __syncthreads();   // previous table fully processed (queues flushed) before the image changes
+            if (threadIdx.x == 0) t = tabs[m];
+            __syncthreads();
+            stage_image(t, smem, op.image_floats(t));
+            staged = m;
+        }
         const SmemView v = make_view(t, smem);
         for (int g0 = a + warp * 32; g0 < b; g0 += kWarpsPerCta * 32) {
             const int64_t g = g0 + lane;

@@ -1,3 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for m in 3 4; do echo "== sample/backward MINB=$m"; MERL_B200_LIB=$PWD/build/libmerl_sb$m.so timeout 300 python tools/quick_perf.py 26 2>&1 | grep -E "^(sample_search0|backward)"; done | tee gpurun_out/quick5.log
+timeout 800 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+python tools/render_bench.py cfg2 --cpu | tee gpurun_out/render_cfg2.json
+python tools/render_bench.py cfg5 100 --cpu | tee gpurun_out/render_cfg5.json
