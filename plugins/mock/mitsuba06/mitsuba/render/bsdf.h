@@ -1,0 +1,2 @@
+#pragma once
+#include <mitsuba/mitsuba.h>  // mock: one header holds everything

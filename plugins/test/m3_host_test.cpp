@@ -1,0 +1,129 @@
+// m3_host_test.cpp -- drives plugins/mitsuba3/{merl,customized_measurment}.cpp the way a Mitsuba 3
+// integrator would (BSDFContext, SurfaceInteraction3f, wo, Mask), built against the mock headers
+// under plugins/mock/mitsuba3 and the real libmerl_b200.  tests/test_gpu_plugins.py feeds it seeded
+// queries and compares what it writes with the CPU oracle.
+//
+//   m3_host_test <plugin: merl|customized_measurment> <table.binary> <queries.bin> <out.bin> [key=value ...]
+//   queries.bin: int64 n, then float32 wi[3][n], wo[3][n], u1[n], u2[2][n], uint8 active[n]
+//   out.bin    : float32 rgb[3][n], pdf[n], eval_only[3][n], pdf_only[n],
+//                s_wo[3][n], s_pdf[n], s_weight[3][n], uint32 s_lobe[n]      (cuda variant, all n)
+//                then the same block for the first min(n, 64) queries through the scalar variant
+#include "../mitsuba3/merl.cpp"
+#include "../mitsuba3/customized_measurment.cpp"
+
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+
+using namespace mitsuba;
+using FloatC = dr::CUDAArray<float>;
+using SpectrumC = Vector<FloatC, 3>;
+using SpectrumS = Vector<float, 3>;
+
+template <typename T> static std::vector<T> read_vec(std::ifstream& f, size_t n) {
+    std::vector<T> v(n);
+    f.read(reinterpret_cast<char*>(v.data()), (std::streamsize) (n * sizeof(T)));
+    if (!f) throw std::runtime_error("short read");
+    return v;
+}
+template <typename T> static void write_vec(std::ofstream& f, const std::vector<T>& v) {
+    f.write(reinterpret_cast<const char*>(v.data()), (std::streamsize) (v.size() * sizeof(T)));
+}
+static std::vector<float> to_host(const FloatC& a) {
+    std::vector<float> h(a.size());
+    dr::store(h.data(), a);
+    return h;
+}
+
+template <typename F, typename S> static std::unique_ptr<BSDF<F, S>> make(const std::string& kind, const Properties& p) {
+    if (kind == "merl") return std::make_unique<MERL<F, S>>(p);
+    if (kind == "customized_measurment") return std::make_unique<CustomizedMeasurment<F, S>>(p);
+    Throw("unknown plugin \"%s\"", kind.c_str());
+}
+
+int main(int argc, char** argv) {
+    if (argc < 5) { std::cerr << "usage: m3_host_test plugin table queries out [key=value ...]\n"; return 2; }
+    try {
+        const std::string kind = argv[1];
+        Properties props;
+        props.set_string("filename", argv[2]);
+        for (int i = 5; i < argc; ++i) {
+            const std::string kv = argv[i];
+            const size_t eq = kv.find('=');
+            if (eq == std::string::npos) Throw("bad parameter \"%s\"", kv.c_str());
+            const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
+            char* end = nullptr;
+            const double d = std::strtod(v.c_str(), &end);
+            if (end && *end == 0 && !v.empty()) props.set_float(k, d); else props.set_string(k, v);
+        }
+        std::ifstream fq(argv[3], std::ios::binary);
+        int64_t n = 0;
+        fq.read(reinterpret_cast<char*>(&n), 8);
+        if (!fq || n < 0) Throw("cannot read %s", argv[3]);
+        const auto wi = read_vec<float>(fq, 3 * n), wo = read_vec<float>(fq, 3 * n), u1 = read_vec<float>(fq, n),
+                   u2 = read_vec<float>(fq, 2 * n);
+        const auto act = read_vec<uint8_t>(fq, n);
+        std::ofstream fo(argv[4], std::ios::binary);
+
+        BSDFContext ctx;
+        {   // ---- cuda_rgb-like variant: whole batch, device arrays ------------------------------
+            auto bsdf = make<FloatC, SpectrumC>(kind, props);
+            std::cout << bsdf->to_string() << std::endl;
+            SurfaceInteraction<FloatC, SpectrumC> si;
+            Vector<FloatC, 3> wod;
+            for (int c = 0; c < 3; ++c) {
+                si.wi.v[c] = dr::load<FloatC>(wi.data() + c * n, n);
+                wod.v[c] = dr::load<FloatC>(wo.data() + c * n, n);
+            }
+            auto active = dr::load<dr::CUDAArray<bool>>(act.data(), n);
+            auto [rgb, pdf] = bsdf->eval_pdf(ctx, si, wod, active);
+            auto rgb_only = bsdf->eval(ctx, si, wod, active);
+            auto pdf_only = bsdf->pdf(ctx, si, wod, active);
+            Vector<FloatC, 2> s2(dr::load<FloatC>(u2.data(), n), dr::load<FloatC>(u2.data() + n, n));
+            auto [bs, weight] = bsdf->sample(ctx, si, dr::load<FloatC>(u1.data(), n), s2, active);
+            dr::sync_thread();
+            for (int c = 0; c < 3; ++c) write_vec(fo, to_host(rgb.v[c]));
+            write_vec(fo, to_host(pdf));
+            for (int c = 0; c < 3; ++c) write_vec(fo, to_host(rgb_only.v[c]));
+            write_vec(fo, to_host(pdf_only));
+            for (int c = 0; c < 3; ++c) write_vec(fo, to_host(bs.wo.v[c]));
+            write_vec(fo, to_host(bs.pdf));
+            for (int c = 0; c < 3; ++c) write_vec(fo, to_host(weight.v[c]));
+            std::vector<uint32_t> lobe(n);
+            dr::store(lobe.data(), static_cast<MeasuredBSDF<FloatC, SpectrumC>*>(bsdf.get())->last_sampled_lobe());
+            write_vec(fo, lobe);
+            // a disabled component yields zeros without touching the device
+            BSDFContext off;
+            off.type_mask = +BSDFFlags::DiffuseReflection;
+            auto z = bsdf->eval(off, si, wod, active);
+            if (dr::width(z.x()) != 1) Throw("disabled component should return a literal zero");
+        }
+        {   // ---- scalar_rgb-like variant: one query per call ------------------------------------
+            auto bsdf = make<float, SpectrumS>(kind, props);
+            const int64_t m = n < 64 ? n : 64;
+            std::vector<float> out(15 * m);
+            std::vector<uint32_t> lobe(m);
+            for (int64_t i = 0; i < m; ++i) {
+                SurfaceInteraction<float, SpectrumS> si;
+                si.wi = Vector<float, 3>(wi[i], wi[n + i], wi[2 * n + i]);
+                const Vector<float, 3> w(wo[i], wo[n + i], wo[2 * n + i]);
+                auto [rgb, pdf] = bsdf->eval_pdf(ctx, si, w, act[i] != 0);
+                auto rgb_only = bsdf->eval(ctx, si, w, act[i] != 0);
+                const float pdf_only = bsdf->pdf(ctx, si, w, act[i] != 0);
+                auto [bs, weight] = bsdf->sample(ctx, si, u1[i], Vector<float, 2>(u2[i], u2[n + i]), act[i] != 0);
+                const float row[15] = { rgb.x(), rgb.y(), rgb.z(), pdf, rgb_only.x(), rgb_only.y(), rgb_only.z(),
+                                        pdf_only, bs.wo.x(), bs.wo.y(), bs.wo.z(), bs.pdf, weight.x(), weight.y(),
+                                        weight.z() };
+                for (int k = 0; k < 15; ++k) out[k * m + i] = row[k];
+                lobe[i] = static_cast<MeasuredBSDF<float, SpectrumS>*>(bsdf.get())->last_sampled_lobe();
+            }
+            write_vec(fo, out);
+            write_vec(fo, lobe);
+        }
+        std::cout << "m3_host_test ok: " << n << " queries, " << merl_launch_count() << " kernel launches" << std::endl;
+        return 0;
+    } catch (const std::exception& e) {
+        std::cerr << "m3_host_test: " << e.what() << std::endl;
+        return 1;
+    }
+}
