@@ -92,6 +92,24 @@ int merl_table_set_cdf(merl_table_t* t, const float* cdf_host);
 /* Copy tables back to the host; any pointer may be NULL.  Synchronous. */
 int merl_table_download(const merl_table_t* t, float* cells4_host, float* cdf_host, float* dens_host);
 
+/* ---- table files either side of the loader ---------------------------------
+ * merl_file_report: host-only scan of a MERL-layout .binary file (header, size, per-channel range,
+ * negative = below-horizon markers, non-finite values); fails with MERL_ERR_IO when the header is
+ * implausible or the size does not match it.  Works without a GPU.
+ * merl_table_save_packed / merl_table_create_from_packed: a sidecar holding the table as it lives
+ * on the device (prescaled float4 cells, sampler CDF rows, the parameters, a checksum), so loading
+ * skips the double -> float4 repack and the CDF quadrature; the resulting table is bit-identical. */
+typedef struct merl_file_report {
+    int32_t dims[3];
+    int32_t is_merl_layout;    /* dims multiply to 90*90*180                                  */
+    int64_t ncell, file_bytes, expected_bytes;
+    int64_t negative[3], nonfinite[3];
+    double min_valid[3], max_valid[3];   /* over finite, non-negative values, raw file units   */
+} merl_file_report_t;
+int merl_file_report(const char* path, merl_file_report_t* out);
+int merl_table_save_packed(const merl_table_t* t, const char* path);
+int merl_table_create_from_packed(const char* path, int device, merl_table_t** out);
+
 /* ---- batched queries, SoA device pointers (rows A1-A6, A10) ----------------------------
  * `active` may be NULL (all lanes active) or a device array of n bytes (Dr.Jit Mask).
  * Lanes that are inactive or have wi.z <= 0 or wo.z <= 0 produce zeros. */

@@ -130,6 +130,9 @@ class MERL:
             if raw.size != 3 * p.nh * p.nd * p.np:
                 raise MerlError(f"data has {raw.size} values, expected 3*{p.nh}*{p.nd}*{p.np}")
             check(_cabi.lib().merl_table_create_from_host(raw.ctypes.data, C.byref(p), dev_index, C.byref(h)))
+        elif "packed" in props:
+            # sidecar written by save_packed(): device-format table + CDF, parameters included
+            check(_cabi.lib().merl_table_create_from_packed(str(props["packed"]).encode(), dev_index, C.byref(h)))
         elif "filename" in props:
             check(_cabi.lib().merl_table_create_from_file(str(props["filename"]).encode(), C.byref(p), dev_index,
                                                           C.byref(h)))
@@ -185,6 +188,10 @@ class MERL:
 
     def dens(self) -> torch.Tensor:
         return torch.as_tensor(_DevArray(self.info.d_dens, (self.info.ni, self.info.nh)), device=self.device)
+
+    def save_packed(self, path):
+        """Write the device-format sidecar (float4 cells + CDF rows + parameters); load with packed=path."""
+        check(_cabi.lib().merl_table_save_packed(self._h, str(path).encode()))
 
     def set_cdf(self, cdf):
         cdf = np.ascontiguousarray(cdf, dtype=np.float32)

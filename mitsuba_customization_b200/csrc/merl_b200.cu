@@ -335,8 +335,12 @@ static void free_table(merl_table* t) {
 
 static void free_pipe(merl_table* t);
 
-static int build_table(const double* planar, const merl_table_params_t* pin, int device, merl_table_t** out) {
-    if (!planar || !out) return fail(MERL_ERR_ARG, "NULL argument");
+// Either `planar` (file-layout doubles: prescale + repack on the device, CDF quadrature on the device)
+// or `cells_host` + `cdf_host` (a packed sidecar: the float4 table and the CDF rows as they were on
+// the device when it was written; uploaded as they are).
+static int build_table(const double* planar, const merl_table_params_t* pin, int device, merl_table_t** out,
+                       const float* cells_host = nullptr, const float* cdf_host = nullptr) {
+    if ((!planar && !(cells_host && cdf_host)) || !out) return fail(MERL_ERR_ARG, "NULL argument");
     merl_table_params_t p;
     if (pin) p = *pin; else merl_table_params_default(&p);
     if (p.nh < 2 || p.nh > kMaxNH || p.nd < 2 || p.nd > kMaxND || p.np < 2 || p.np > kMaxNP)
@@ -420,8 +424,12 @@ static int build_table(const double* planar, const merl_table_params_t* pin, int
     TRY_OR_BAIL(cudaMalloc(&t->d_cells, sizeof(float4) * t->ncell));
     TRY_OR_BAIL(cudaMalloc(&t->d_image, sizeof(float) * img.size()));
     TRY_OR_BAIL(cudaMalloc(&t->d_edges64, sizeof(double) * n64));
-    TRY_OR_BAIL(cudaMalloc(&d_raw, sizeof(double) * 3 * t->ncell));
-    TRY_OR_BAIL(cudaMemcpyAsync(d_raw, planar, sizeof(double) * 3 * t->ncell, cudaMemcpyHostToDevice, s));
+    if (planar) {
+        TRY_OR_BAIL(cudaMalloc(&d_raw, sizeof(double) * 3 * t->ncell));
+        TRY_OR_BAIL(cudaMemcpyAsync(d_raw, planar, sizeof(double) * 3 * t->ncell, cudaMemcpyHostToDevice, s));
+    } else {
+        TRY_OR_BAIL(cudaMemcpyAsync(t->d_cells, cells_host, sizeof(float4) * t->ncell, cudaMemcpyHostToDevice, s));
+    }
     TRY_OR_BAIL(cudaMemcpyAsync(t->d_image, img.data(), sizeof(float) * img.size(), cudaMemcpyHostToDevice, s));
     TRY_OR_BAIL(cudaMemcpyAsync(t->d_edges64, e64.data(), sizeof(double) * n64, cudaMemcpyHostToDevice, s));
     d.cells = t->d_cells;
@@ -430,11 +438,13 @@ static int build_table(const double* planar, const merl_table_params_t* pin, int
     d.thr_h64 = t->d_edges64 + 2 * (p.np + 1);
     d.thr_d64 = d.thr_h64 + p.nh + 1;
     t->d_medge64 = const_cast<double*>(d.thr_d64) + p.nd + 1;
-    repack_kernel<<<t->num_sms * 4, 256, 0, s>>>(d_raw, t->ncell, p.scale[0], p.scale[1], p.scale[2],
-                                                 p.clamp_negative, t->d_cells);
-    TRY_OR_BAIL(cudaGetLastError());
-    g_launches.fetch_add(1);
-    rc = upload_sampler(t, nullptr, s);
+    if (planar) {
+        repack_kernel<<<t->num_sms * 4, 256, 0, s>>>(d_raw, t->ncell, p.scale[0], p.scale[1], p.scale[2],
+                                                     p.clamp_negative, t->d_cells);
+        TRY_OR_BAIL(cudaGetLastError());
+        g_launches.fetch_add(1);
+    }
+    rc = upload_sampler(t, planar ? nullptr : cdf_host, s);
     if (rc) return bail(rc);
     TRY_OR_BAIL(cudaStreamSynchronize(s));
     cudaFree(d_raw);
@@ -529,6 +539,118 @@ extern "C" int merl_table_download(const merl_table_t* t, float* cells4, float* 
     if (cdf) CUDA_TRY(cudaMemcpy(cdf, t->d_image + d.off_cdf, sizeof(float) * d.ni * (d.nh + 1), cudaMemcpyDeviceToHost));
     if (dens) CUDA_TRY(cudaMemcpy(dens, t->d_image + d.off_dens, sizeof(float) * d.ni * d.nh, cudaMemcpyDeviceToHost));
     return MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// table files either side of the loader: a report on a .binary file, and a
+// packed sidecar that holds the device-format table so a scene with many tables starts fast
+// ------------------------------------------------------------------------------------------
+extern "C" int merl_file_report(const char* path, merl_file_report_t* o) {
+    if (!path || !o) return fail(MERL_ERR_ARG, "NULL argument");
+    memset(o, 0, sizeof *o);
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(MERL_ERR_IO, "cannot open '%s'", path);
+    if (fread(o->dims, sizeof(int32_t), 3, f) != 3) { fclose(f); return fail(MERL_ERR_IO, "'%s': short header", path); }
+    fseek(f, 0, SEEK_END);
+    o->file_bytes = (int64_t)ftell(f);
+    fseek(f, 12, SEEK_SET);
+    const int64_t n = (int64_t)o->dims[0] * o->dims[1] * o->dims[2];
+    o->ncell = n;
+    o->is_merl_layout = (n == 90 * 90 * 180);
+    if (o->dims[0] <= 0 || o->dims[1] <= 0 || o->dims[2] <= 0 || n > ((int64_t)1 << 31)) {
+        fclose(f);
+        return fail(MERL_ERR_IO, "'%s': implausible header %d x %d x %d", path, o->dims[0], o->dims[1], o->dims[2]);
+    }
+    o->expected_bytes = 12 + 3 * n * 8;
+    if (o->file_bytes != o->expected_bytes) {
+        fclose(f);
+        return fail(MERL_ERR_IO, "'%s': %lld bytes, a %d x %d x %d table needs %lld", path, (long long)o->file_bytes,
+                    o->dims[0], o->dims[1], o->dims[2], (long long)o->expected_bytes);
+    }
+    std::vector<double> buf((size_t)1 << 16);
+    for (int c = 0; c < 3; ++c) {
+        double mn = INFINITY, mx = -INFINITY;
+        int64_t left = n;
+        while (left > 0) {
+            const size_t want = (size_t)(left < (int64_t)buf.size() ? left : (int64_t)buf.size());
+            if (fread(buf.data(), 8, want, f) != want) { fclose(f); return fail(MERL_ERR_IO, "'%s': read error", path); }
+            for (size_t i = 0; i < want; ++i) {
+                const double v = buf[i];
+                if (!(v == v) || v == INFINITY || v == -INFINITY) { o->nonfinite[c]++; continue; }
+                if (v < 0.0) { o->negative[c]++; continue; }       // MERL marks below-horizon cells with negatives
+                mn = v < mn ? v : mn;
+                mx = v > mx ? v : mx;
+            }
+            left -= (int64_t)want;
+        }
+        o->min_valid[c] = mn;
+        o->max_valid[c] = mx;
+    }
+    fclose(f);
+    return MERL_OK;
+}
+
+namespace {
+struct PackedHeader {
+    char magic[8];               // "MERLB200"
+    int32_t version, header_bytes;
+    merl_table_params_t params;
+    int64_t ncell, cdf_floats;
+    uint64_t checksum;           // FNV-1a over the payload
+};
+constexpr int32_t kPackedVersion = 1;
+uint64_t fnv1a(const void* p, size_t n, uint64_t h) {
+    const unsigned char* c = static_cast<const unsigned char*>(p);
+    for (size_t i = 0; i < n; ++i) { h ^= c[i]; h *= 1099511628211ull; }
+    return h;
+}
+}  // namespace
+
+extern "C" int merl_table_save_packed(const merl_table_t* t, const char* path) {
+    if (!t || !path) return fail(MERL_ERR_ARG, "NULL argument");
+    const TableDev& d = t->dev;
+    std::vector<float> cells((size_t)4 * t->ncell), cdf((size_t)d.ni * (d.nh + 1));
+    const int rc = merl_table_download(t, cells.data(), cdf.data(), nullptr);
+    if (rc) return rc;
+    PackedHeader h{};
+    memcpy(h.magic, "MERLB200", 8);
+    h.version = kPackedVersion;
+    h.header_bytes = (int32_t)sizeof h;
+    h.params = t->params;
+    h.ncell = t->ncell;
+    h.cdf_floats = (int64_t)cdf.size();
+    h.checksum = fnv1a(cdf.data(), cdf.size() * 4, fnv1a(cells.data(), cells.size() * 4, 1469598103934665603ull));
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(MERL_ERR_IO, "cannot create '%s'", path);
+    const bool ok = fwrite(&h, sizeof h, 1, f) == 1 && fwrite(cells.data(), 4, cells.size(), f) == cells.size() &&
+                    fwrite(cdf.data(), 4, cdf.size(), f) == cdf.size();
+    if (fclose(f) != 0 || !ok) return fail(MERL_ERR_IO, "'%s': write error", path);
+    return MERL_OK;
+}
+
+extern "C" int merl_table_create_from_packed(const char* path, int device, merl_table_t** out) {
+    if (!path || !out) return fail(MERL_ERR_ARG, "NULL argument");
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(MERL_ERR_IO, "cannot open '%s'", path);
+    PackedHeader h{};
+    if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "MERLB200", 8) != 0) {
+        fclose(f);
+        return fail(MERL_ERR_IO, "'%s' is not a packed libmerl_b200 table", path);
+    }
+    const merl_table_params_t& p = h.params;
+    if (h.version != kPackedVersion || h.header_bytes != (int32_t)sizeof h || p.nh < 2 || p.nh > kMaxNH || p.nd < 2 ||
+        p.nd > kMaxND || p.np < 2 || p.np > kMaxNP || p.ni < 1 || p.ni > kMaxNI ||
+        h.ncell != (int64_t)p.nh * p.nd * p.np || h.cdf_floats != (int64_t)p.ni * (p.nh + 1)) {
+        fclose(f);
+        return fail(MERL_ERR_IO, "'%s': unsupported version or inconsistent header", path);
+    }
+    std::vector<float> cells((size_t)4 * h.ncell), cdf((size_t)h.cdf_floats);
+    const bool ok = fread(cells.data(), 4, cells.size(), f) == cells.size() && fread(cdf.data(), 4, cdf.size(), f) == cdf.size();
+    fclose(f);
+    if (!ok) return fail(MERL_ERR_IO, "'%s' is truncated", path);
+    if (fnv1a(cdf.data(), cdf.size() * 4, fnv1a(cells.data(), cells.size() * 4, 1469598103934665603ull)) != h.checksum)
+        return fail(MERL_ERR_IO, "'%s': checksum mismatch", path);
+    return build_table(nullptr, &p, device, out, cells.data(), cdf.data());
 }
 
 // ------------------------------------------------------------------------------------------

@@ -35,6 +35,18 @@ template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g,
 template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g, const Pack<4>& a) {
     __stcs(reinterpret_cast<float4*>(p) + g, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
 }
+// L2 prefetch of the 16 B (VEC = 4) a lane will stream MERL_PREFETCH iterations from now: moves the
+// HBM latency off the load's critical path at no register cost.  MERL_PREFETCH_SPARSE: one lane per
+// 128-byte line issues it instead of all eight.
+#ifndef MERL_PREFETCH
+#define MERL_PREFETCH 0
+#endif
+#ifndef MERL_PREFETCH_SPARSE
+#define MERL_PREFETCH_SPARSE 0
+#endif
+template <int VEC> __device__ __forceinline__ void prefetch_stream(const float* p, int64_t g) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + g * VEC));
+}
 template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
 template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
     return p ? (p[g] != 0) : 1u;
@@ -103,6 +115,12 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
     // warp-uniform trip count: flush and some ops use warp-level synchronisation
     for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
         const int64_t g = g0 + lane;
+#if MERL_PREFETCH
+        {
+            const int64_t gp = g + stride * MERL_PREFETCH;
+            if (gp < ngroups && (!MERL_PREFETCH_SPARSE || (lane & (Op::kVec == 4 ? 7 : 31)) == 0)) op.prefetch(gp);
+        }
+#endif
         const unsigned m = op.hot(t, v, g, g < ngroups, lane);
         if (m) {
 #pragma unroll
@@ -149,6 +167,10 @@ struct QueryOp {
     QueryOut out;
 
     __device__ __forceinline__ int image_floats(const TableDev& t) const { return kPdf ? t.image_eval_floats : t.off_dens; }
+    __device__ __forceinline__ void prefetch(const int64_t g) const {
+        prefetch_stream<VEC>(in.wix, g); prefetch_stream<VEC>(in.wiy, g); prefetch_stream<VEC>(in.wiz, g);
+        prefetch_stream<VEC>(in.wox, g); prefetch_stream<VEC>(in.woy, g); prefetch_stream<VEC>(in.woz, g);
+    }
 
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int) const {
@@ -222,23 +244,6 @@ struct QueryOp {
 // ------------------------------------------------------------------------------------------
 // sample   (row A6; oracle: draw_direction + eval_pdf_one)
 // ------------------------------------------------------------------------------------------
-// Mitsuba 3's concentric square->disk map, lifted to the cosine-weighted hemisphere.
-__device__ __forceinline__ void cosine_hemisphere(float ux, float uy, float& x, float& y, float& z) {
-    const float sx = fmaf(2.f, ux, -1.f), sy = fmaf(2.f, uy, -1.f);
-    const bool q13 = fabsf(sx) < fabsf(sy);
-    const float r = q13 ? sy : sx, rp = q13 ? sx : sy;
-    float ph = 0.25f * __fdividef(rp, r);            // in units of pi
-    if (q13) ph = 0.5f - ph;
-    if (sx == 0.f && sy == 0.f) ph = 0.f;
-    float s, c;
-    sincospif(ph, &s, &c);
-    x = r * c; y = r * s;
-    // z^2 = 1 - x^2 - y^2 = 1 - r^2, factored so that it keeps full relative accuracy at the
-    // horizon (r -> 1), where the subtraction of squares would cancel in fp32
-    const float ar = fabsf(r);
-    z = sqrtf(fmaxf(0.f, (1.f - ar) * (1.f + ar)));
-}
-
 // Largest i in [0, nh-1] with row[i] <= u (row[0] = 0).  Per-lane, fixed trip count (no
 // divergence): descending power-of-two strides over the smem-resident row.
 __device__ __forceinline__ int search_lane(const float* row, int nh, int step0, float u) {
@@ -274,21 +279,39 @@ __device__ __forceinline__ int search_warp_coop(const float* cdf, int nh, int my
     return result;
 }
 
-// wo of the tabulated half-vector lobe: theta_h bin i of slice j, solid-angle-uniform inside the
-// bin, phi_h = 2 pi uy; wo = reflect(wi, h).
-__device__ __forceinline__ void spec_direction(const SmemView& v, const float* row, int i, float ax, float ay,
-                                               float az, float ux, float uy, float& x, float& y, float& z) {
+// wo of either lobe with ONE sincospi and ONE sqrt: both lobes are "radius * (cos, sin)(angle)
+// plus a height", so the lobe only selects the angle and the radicand (the unselected lobe's
+// values are never formed).  Per lobe this is the oracle's draw_direction: cosine lobe = Mitsuba 3's
+// concentric square->disk map lifted to the hemisphere, (x, y, z) = (r c, r s, sqrt((1-|r|)(1+|r|)))
+// (z^2 = 1 - r^2 factored so that it keeps full relative accuracy at the horizon); tabulated
+// lobe h = (st c, st s, 1 - m) with st = sqrt(m (2 - m)), theta_h bin i of the slice's CDF row,
+// solid-angle-uniform inside the bin, phi_h = 2 pi uy, and wo = reflect(wi, h).
+__device__ __forceinline__ void draw_direction(const SmemView& v, const float* row, int i, bool spec, float ax,
+                                               float ay, float az, float ux, float uy, float& x, float& y, float& z) {
+    // cosine lobe: concentric square -> disk
+    const float sx = fmaf(2.f, ux, -1.f), sy = fmaf(2.f, uy, -1.f);
+    const bool q13 = fabsf(sx) < fabsf(sy);
+    const float r = q13 ? sy : sx, rp = q13 ? sx : sy;
+    float ph = 0.25f * __fdividef(rp, r);            // in units of pi
+    if (q13) ph = 0.5f - ph;
+    if (sx == 0.f && sy == 0.f) ph = 0.f;
+    const float ar = fabsf(r);
+    // tabulated lobe: position inside theta_h bin i
     const float c0 = row[i], c1 = row[i + 1];
     const float w = c1 - c0;
     const float f = w > 0.f ? __fdividef(ux - c0, w) : 0.5f;
     const float m0 = v.medge[i], m1 = v.medge[i + 1];
     const float m = fmaf(f, m1 - m0, m0);
-    const float ct = 1.f - m, st = sqrtf(m * (2.f - m));
-    float sp, cp;
-    sincospif(2.f * uy, &sp, &cp);
-    const float hx = st * cp, hy = st * sp, hz = ct;
-    const float c2 = 2.f * fmaf(ax, hx, fmaf(ay, hy, az * hz));
-    x = fmaf(c2, hx, -ax); y = fmaf(c2, hy, -ay); z = fmaf(c2, hz, -az);
+    // shared transcendental work
+    float sn, cs;
+    sincospif(spec ? 2.f * uy : ph, &sn, &cs);
+    const float root = sqrtf(spec ? m * (2.f - m) : fmaxf(0.f, (1.f - ar) * (1.f + ar)));
+    const float rad = spec ? root : r;
+    const float px = rad * cs, py = rad * sn, pz = spec ? 1.f - m : root;   // cosine: wo; tabulated: h
+    const float c2 = 2.f * fmaf(ax, px, fmaf(ay, py, az * pz));
+    x = spec ? fmaf(c2, px, -ax) : px;
+    y = spec ? fmaf(c2, py, -ay) : py;
+    z = spec ? fmaf(c2, pz, -az) : pz;
 }
 
 struct SampleIn {
@@ -307,6 +330,10 @@ struct SampleOp {
     SampleOut out;
 
     __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.image_full_floats; }
+    __device__ __forceinline__ void prefetch(const int64_t g) const {
+        prefetch_stream<VEC>(in.wix, g); prefetch_stream<VEC>(in.wiy, g); prefetch_stream<VEC>(in.wiz, g);
+        prefetch_stream<VEC>(in.u1, g); prefetch_stream<VEC>(in.u2x, g); prefetch_stream<VEC>(in.u2y, g);
+    }
 
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int lane) const {
@@ -326,14 +353,12 @@ struct SampleOp {
             const bool ok = ((act >> q) & 1u) && az.v[q] > 0.f;
             const bool spec = u1.v[q] < t.spec_weight;
             lobe[q] = (ok && spec) ? 1u : 0u;
-            float x, y, z, sx, sy, sz;
-            cosine_hemisphere(ux.v[q], uy.v[q], x, y, z);
+            float x, y, z;
             const int j = max(min((int)(az.v[q] * (float)t.ni), t.ni - 1), 0);
             const float* row = v.cdf + j * (t.nh + 1);
             const int i = SEARCH ? search_warp_coop(v.cdf, t.nh, j, ux.v[q], ok && spec, (unsigned)lane)
                                  : search_lane(row, t.nh, t.search_step, ux.v[q]);
-            spec_direction(v, row, i, ax.v[q], ay.v[q], az.v[q], ux.v[q], uy.v[q], sx, sy, sz);
-            x = spec ? sx : x; y = spec ? sy : y; z = spec ? sz : z;
+            draw_direction(v, row, i, spec, ax.v[q], ay.v[q], az.v[q], ux.v[q], uy.v[q], x, y, z);
             valid[q] = ok && z > 0.f;
             const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], x, y, z);
             unsigned unc;
@@ -401,6 +426,11 @@ struct BackwardOp {
     float4* grad;
 
     __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.off_dens; }
+    __device__ __forceinline__ void prefetch(const int64_t g) const {
+        prefetch_stream<VEC>(q.wix, g); prefetch_stream<VEC>(q.wiy, g); prefetch_stream<VEC>(q.wiz, g);
+        prefetch_stream<VEC>(q.wox, g); prefetch_stream<VEC>(q.woy, g); prefetch_stream<VEC>(q.woz, g);
+        prefetch_stream<VEC>(gr, g); prefetch_stream<VEC>(gg, g); prefetch_stream<VEC>(gb, g);
+    }
 
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int lane) const {
@@ -485,6 +515,9 @@ struct EvalPdfAosOp {
     float4* out4;
 
     __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.image_eval_floats; }
+    __device__ __forceinline__ void prefetch(const int64_t g) const {
+        prefetch_stream<4>(reinterpret_cast<const float*>(wi4), g); prefetch_stream<4>(reinterpret_cast<const float*>(wo4), g);
+    }
 
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int) const {
@@ -516,6 +549,9 @@ struct SampleAosOp {
     float4 *wo4, *w4;
 
     __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.image_full_floats; }
+    __device__ __forceinline__ void prefetch(const int64_t g) const {
+        prefetch_stream<4>(reinterpret_cast<const float*>(wi4), g); prefetch_stream<4>(reinterpret_cast<const float*>(u4), g);
+    }
 
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int) const {
@@ -523,13 +559,11 @@ struct SampleAosOp {
         const float4 a = __ldcs(wi4 + g), u = __ldcs(u4 + g);
         const bool ok = a.z > 0.f;
         const bool spec = u.x < t.spec_weight;
-        float x, y, z, sx, sy, sz;
-        cosine_hemisphere(u.y, u.z, x, y, z);
+        float x, y, z;
         const int j = max(min((int)(a.z * (float)t.ni), t.ni - 1), 0);
         const float* row = v.cdf + j * (t.nh + 1);
         const int i = search_lane(row, t.nh, t.search_step, u.y);
-        spec_direction(v, row, i, a.x, a.y, a.z, u.y, u.z, sx, sy, sz);
-        x = spec ? sx : x; y = spec ? sy : y; z = spec ? sz : z;
+        draw_direction(v, row, i, spec, a.x, a.y, a.z, u.y, u.z, x, y, z);
         const bool valid = ok && z > 0.f;
         const HalfDiff h = half_diff_setup(a.x, a.y, a.z, x, y, z);
         unsigned unc;
