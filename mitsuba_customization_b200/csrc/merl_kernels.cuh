@@ -35,15 +35,11 @@ template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g,
 template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g, const Pack<4>& a) {
     __stcs(reinterpret_cast<float4*>(p) + g, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
 }
-// L2 prefetch of the 16 B (VEC = 4) a lane will stream MERL_PREFETCH iterations from now: moves the
-// HBM latency off the load's critical path at no register cost.  MERL_PREFETCH_SPARSE: one lane per
-// 128-byte line issues it instead of all eight.
-#ifndef MERL_PREFETCH
-#define MERL_PREFETCH 0
-#endif
-#ifndef MERL_PREFETCH_SPARSE
-#define MERL_PREFETCH_SPARSE 0
-#endif
+// L2 prefetch of what a lane will stream Op::kPrefetch iterations from now: moves the HBM latency off
+// the load's critical path at no register cost.  Measured on B200 (2^26 queries, profiles/
+// r01_tuning.md): eval+pdf 109 -> 117 Gquery/s, eval 125 -> 131 at distance 1; distance 2 is no better;
+// the sample and backward kernels (more streams per query, so more L2 pressure per iteration) lose
+// 1-5 %, so only the query kernels use it.
 template <int VEC> __device__ __forceinline__ void prefetch_stream(const float* p, int64_t g) {
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p + g * VEC));
 }
@@ -96,6 +92,7 @@ __device__ __forceinline__ void flush_queue(const Op& op, const TableDev& t, con
 
 // Op interface:
 //   static constexpr int kVec       queries per lane and iteration
+//   static constexpr int kPrefetch  L2 prefetch distance in iterations (0 = none); void prefetch(g)
 //   int image_floats(t)             floats of the table image the op needs in shared memory
 //   unsigned hot(t, v, g, in_range, lane)   tier-1 pass over group g (called by every lane of the
 //                                   warp, so ops may use warp collectives); returns bit q set
@@ -115,12 +112,10 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
     // warp-uniform trip count: flush and some ops use warp-level synchronisation
     for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
         const int64_t g = g0 + lane;
-#if MERL_PREFETCH
-        {
-            const int64_t gp = g + stride * MERL_PREFETCH;
-            if (gp < ngroups && (!MERL_PREFETCH_SPARSE || (lane & (Op::kVec == 4 ? 7 : 31)) == 0)) op.prefetch(gp);
+        if (Op::kPrefetch > 0) {
+            const int64_t gp = g + stride * Op::kPrefetch;
+            if (gp < ngroups) op.prefetch(gp);
         }
-#endif
         const unsigned m = op.hot(t, v, g, g < ngroups, lane);
         if (m) {
 #pragma unroll
@@ -161,6 +156,10 @@ struct QueryOut {
 template <int MODE, int VEC>
 struct QueryOp {
     static constexpr int kVec = VEC;
+#ifndef MERL_PF_QUERY
+#define MERL_PF_QUERY 1
+#endif
+    static constexpr int kPrefetch = MERL_PF_QUERY;
     static constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
     static constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
     QueryIn in;
@@ -326,6 +325,10 @@ struct SampleOut {
 template <int VEC, int SEARCH>
 struct SampleOp {
     static constexpr int kVec = VEC;
+#ifndef MERL_PF_SAMPLE
+#define MERL_PF_SAMPLE 0
+#endif
+    static constexpr int kPrefetch = MERL_PF_SAMPLE;
     SampleIn in;
     SampleOut out;
 
@@ -421,6 +424,10 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
 template <int VEC, int AGG>
 struct BackwardOp {
     static constexpr int kVec = VEC;
+#ifndef MERL_PF_BACKWARD
+#define MERL_PF_BACKWARD 0
+#endif
+    static constexpr int kPrefetch = MERL_PF_BACKWARD;
     QueryIn q;
     const float *gr, *gg, *gb;
     float4* grad;
@@ -511,6 +518,7 @@ struct BackwardOp {
 // ------------------------------------------------------------------------------------------
 struct EvalPdfAosOp {
     static constexpr int kVec = 1;
+    static constexpr int kPrefetch = 0;
     const float4 *wi4, *wo4;
     float4* out4;
 
@@ -545,6 +553,7 @@ struct EvalPdfAosOp {
 
 struct SampleAosOp {
     static constexpr int kVec = 1;
+    static constexpr int kPrefetch = 0;
     const float4 *wi4, *u4;
     float4 *wo4, *w4;
 
