@@ -129,9 +129,11 @@ __device__ __noinline__ void resolve_bins_slow(const TableDev& t, float ax_, flo
                                                float bx_, float by_, float bz_, int kh, int kd, int kp,
                                                unsigned unc, Bins& out);
 
-// Tier 1.  Returns the tier-1 bins and, in `unc`, which coordinates (bit 0/1/2 = theta_h /
-// theta_d / phi_d) were decided inside their error margin and therefore need tiers 2-3.
+// Tier 1.  Returns the tier-1 bins and, in `unc`, whether any coordinate was decided inside its
+// error margin and therefore needs tiers 2-3: nonzero / zero when DETAIL is false (the streaming
+// loops), which coordinates (bit 0/1/2 = theta_h / theta_d / phi_d) when DETAIL is true (the redo).
 // kc[] receives the candidate edges the slow tiers start from.
+template <bool DETAIL = false>
 __device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemView& v, float ax, float ay,
                                                   float az, float bx, float by, float bz, const HalfDiff& h,
                                                   unsigned& unc, int kc[3]) {
@@ -156,15 +158,27 @@ __device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemV
     b.ih = max(min(kh - 1 + (dh >= 0.f), t.nh - 1), 0);  // max(): NaN inputs must not index out of range
     b.id = max(min(kd - 1 + (dd >= 0.f), t.nd - 1), 0);
     b.ip = max(min(kp - 1 + (dp >= 0.f), t.np - 1), 0);
-    // (bitwise, not short-circuit: the streaming loop must stay branch-free so that the four
-    // queries a thread holds interleave)
+    // Certainty: every comparison must clear its error margin, and for phi_d |(X,Y)| must also be
+    // large enough that the same error cannot have moved the candidate edge itself by half a bin.
+    // All four conditions are "slack > 0", so one min and one compare decide them together
+    // (branch-free: the four queries a thread holds must keep interleaving).  No k == 0 / k == n
+    // guards are needed: the edge tables hold 0 / +inf (theta_h) and 4 / -4 (theta_d) there, which
+    // puts |d| far outside the margin, and the clamp above makes the bin independent of d.
+    // fminf drops NaN operands, so non-finite inputs are caught by the test on n2 instead.
     const float mp = EPS_P * (h.n2 + h.slen);
-    const bool uh = (kh > 0) & (kh < t.nh) & !(fabsf(dh) > EPS_H * h.rho2);
-    const bool ud = (kd > 0) & (kd < t.nd) & !(fabsf(dd) > EPS_D * h.n2);
-    // phi_d: the comparison must clear its error margin AND |(X,Y)| must be large enough that
-    // the same error cannot have moved the candidate edge itself by half a bin.
-    const bool up = !(fabsf(dp) > mp) | !(fabsf(X) + Y > mp * 4.f * (float)t.np);
-    unc = (unsigned)uh | ((unsigned)ud << 1) | ((unsigned)up << 2);
+    const float slack_h = fmaf(-EPS_H, h.rho2, fabsf(dh));
+    const float slack_d = fmaf(-EPS_D, h.n2, fabsf(dd));
+    const float slack_p = fabsf(dp) - mp;
+    const float slack_c = fmaf(-4.f * (float)t.np, mp, fabsf(X) + Y);
+    const bool finite = h.n2 < __int_as_float(0x7f800000);
+    if (DETAIL) {   // which coordinate(s): only the slow tiers need to know
+        const unsigned all = finite ? 0u : 7u;
+        unc = all | (unsigned)!(slack_h > 0.f) | ((unsigned)!(slack_d > 0.f) << 1) |
+              ((unsigned)(!(slack_p > 0.f) | !(slack_c > 0.f)) << 2);
+    } else {
+        const float slack = fminf(fminf(slack_h, slack_d), fminf(slack_p, slack_c));
+        unc = (unsigned)(!(slack > 0.f) | !finite);
+    }
     kc[0] = kh; kc[1] = kd; kc[2] = kp;
     return b;
 }
@@ -175,7 +189,7 @@ __device__ __forceinline__ Bins compute_bins(const TableDev& t, const SmemView& 
                                              float az, float bx, float by, float bz, const HalfDiff& h) {
     unsigned unc;
     int kc[3];
-    Bins b = compute_bins_fast(t, v, ax, ay, az, bx, by, bz, h, unc, kc);
+    Bins b = compute_bins_fast<true>(t, v, ax, ay, az, bx, by, bz, h, unc, kc);
     if (unc) resolve_bins_slow(t, ax, ay, az, bx, by, bz, kc[0], kc[1], kc[2], unc, b);
     return b;
 }
