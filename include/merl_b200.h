@@ -178,7 +178,7 @@ typedef struct merl_render_params {
     int32_t spp_total;         /* normalisation                                         */
     int32_t spp_begin, spp_end;/* sample indices this call renders for every pixel       */
     int32_t max_depth;         /* surface interactions per path (>= 1)                   */
-    int32_t wavefront;         /* paths per pass; 0 = 1 << 21                            */
+    int32_t wavefront;         /* paths per pass; 0 = 1 << 23 (2 GB of workspace) */
     int32_t reserved;
     uint64_t seed;
     float cam_pos[3], cam_target[3], cam_up[3];
@@ -193,6 +193,10 @@ typedef struct merl_render_stats {
 int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres_host, int nspheres,
                 const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out /* may be NULL */,
                 merl_stream_t stream);
+
+/* merl_render replays one CUDA graph per wavefront pass (default).  0 = enqueue every kernel on the
+ * caller's stream instead (same results; for A/B timing and for hosts that are themselves capturing). */
+int merl_set_render_graphs(int on);
 
 /* ---- multi-GPU exchange step: table gradients and film buffers --------------
  * The forward path shards by query batch with no collective.  The backward path keeps a private

@@ -18,7 +18,7 @@ SYMBOLS = [
     "merl_file_report", "merl_table_save_packed", "merl_table_create_from_packed",
     "merl_bins", "merl_eval", "merl_pdf", "merl_eval_pdf", "merl_sample", "merl_backward",
     "merl_eval_pdf_aos", "merl_sample_aos", "merl_eval_pdf_host", "merl_sample_host",
-    "merl_render",
+    "merl_render", "merl_set_render_graphs",
     "merl_comm_unique_id", "merl_comm_create", "merl_comm_destroy", "merl_allreduce_sum_f32",
     "merl_last_error", "merl_abi_version", "merl_launch_count", "merl_set_sample_search",
 ]
@@ -95,6 +95,7 @@ def lib():
         L.merl_eval_pdf_host.argtypes = [vp] + [vp] * 6 + [i64] + [vp] * 4
         L.merl_sample_host.argtypes = [vp] + [vp] * 6 + [i64] + [vp] * 8
         L.merl_set_sample_search.argtypes = [i32]
+        L.merl_set_render_graphs.argtypes = [i32]
         L.merl_render.argtypes = [vp, i32, vp, i32, vp, vp, vp, vp]
         L.merl_comm_unique_id.argtypes = [vp]
         L.merl_comm_create.argtypes = [vp, i32, i32, i32, C.POINTER(vp)]

@@ -11,6 +11,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <cmath>
+#include <utility>
 #include <atomic>
 #include <mutex>
 #include <string>
@@ -24,11 +27,14 @@
 using namespace merl;
 
 // resident CTAs per SM the register allocation of the 4-wide sample / backward ops is capped for
+#ifndef MERL_QUERY_MINB
+#define MERL_QUERY_MINB (3 * kMinbScale)
+#endif
 #ifndef MERL_SAMPLE_MINB
-#define MERL_SAMPLE_MINB 3
+#define MERL_SAMPLE_MINB (3 * kMinbScale)
 #endif
 #ifndef MERL_BWD_MINB
-#define MERL_BWD_MINB 3
+#define MERL_BWD_MINB (3 * kMinbScale)
 #endif
 
 // ------------------------------------------------------------------------------------------
@@ -201,7 +207,8 @@ __global__ void dens_kernel(const float* __restrict__ cdf, const double* __restr
 // ------------------------------------------------------------------------------------------
 // host: launch plumbing
 // ------------------------------------------------------------------------------------------
-static constexpr int kThreads = 256;
+static constexpr int kThreads = kThreadsPerCta;
+static constexpr int kMinbScale = 256 / kThreadsPerCta;   // MINB values below are per 256-thread CTA
 static constexpr size_t kMaxSmemBytes = 100 * 1024;   // per-table image (edges, densities, CDF rows)
 
 template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
@@ -279,12 +286,12 @@ static int run_query_mode(const merl_table* t, const QueryIn& in, int64_t n, con
                      aligned(out.g, 16) && aligned(out.b, 16) && aligned(out.pdf, 16) && aligned(out.idx, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_op<QueryOp<MODE, 4>, 3>(t, QueryOp<MODE, 4>{in, out}, fl, n / 4, s);
+        const int rc = launch_op<QueryOp<MODE, 4>, MERL_QUERY_MINB>(t, QueryOp<MODE, 4>{in, out}, fl, n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;
     }
     if (done < n)
-        return launch_op<QueryOp<MODE, 1>, 4>(t, QueryOp<MODE, 1>{offset_in(in, done), offset_out(out, done)}, fl,
+        return launch_op<QueryOp<MODE, 1>, 4 * kMinbScale>(t, QueryOp<MODE, 1>{offset_in(in, done), offset_out(out, done)}, fl,
                                               n - done, s);
     return MERL_OK;
 }
@@ -722,7 +729,7 @@ static int run_sample(const merl_table* t, SampleIn in, int64_t n, SampleOut out
         if (in.active) in.active += done;
         out.wox += done; out.woy += done; out.woz += done; out.pdf += done;
         out.wr += done; out.wg += done; out.wb += done; out.lobe += done;
-        return launch_op<SampleOp<1, SEARCH>, 3>(t, SampleOp<1, SEARCH>{in, out}, fl, n - done, s);
+        return launch_op<SampleOp<1, SEARCH>, 3 * kMinbScale>(t, SampleOp<1, SEARCH>{in, out}, fl, n - done, s);
     }
     return MERL_OK;
 }
@@ -764,7 +771,7 @@ static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* g
     if (done < n) {
         in.q = offset_in(in.q, done);
         in.gr += done; in.gg += done; in.gb += done;
-        return launch_op<BackwardOp<1, AGG>, 3>(t, BackwardOp<1, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done,
+        return launch_op<BackwardOp<1, AGG>, 3 * kMinbScale>(t, BackwardOp<1, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done,
                                                 s);
     }
     return MERL_OK;
@@ -793,7 +800,7 @@ extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const 
     DeviceGuard gd(t->device);
     const EvalPdfAosOp op{reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(wo4),
                           reinterpret_cast<float4*>(out4)};
-    return launch_op<EvalPdfAosOp, 4>(t, op, t->dev.image_eval_floats, n, (cudaStream_t)stream);
+    return launch_op<EvalPdfAosOp, 4 * kMinbScale>(t, op, t->dev.image_eval_floats, n, (cudaStream_t)stream);
 }
 
 extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const float* u4, int64_t n, float* wo4_out,
@@ -804,7 +811,7 @@ extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const fl
     DeviceGuard gd(t->device);
     const SampleAosOp op{reinterpret_cast<const float4*>(wi4), reinterpret_cast<const float4*>(u4),
                          reinterpret_cast<float4*>(wo4_out), reinterpret_cast<float4*>(weight4_out)};
-    return launch_op<SampleAosOp, 3>(t, op, t->dev.image_full_floats, n, (cudaStream_t)stream);
+    return launch_op<SampleAosOp, 3 * kMinbScale>(t, op, t->dev.image_full_floats, n, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1011,6 +1018,92 @@ static void cross3(const float a[3], const float b[3], float o[3]) {
     o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
 }
 
+// Side stream + cached pass graph of merl_render, one per device.  Instantiating a graph costs far
+// more than launching it, so the executable graph of the last call is kept and re-targeted with
+// cudaGraphExecUpdate (same topology, new pointers / parameters); only a topology change (another
+// max_depth) instantiates again.  A replaced executable must outlive its last launch; instead of
+// synchronising, it is destroyed by a later call once its event has completed.
+struct RenderSide {
+    std::mutex mu;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    struct Retired { cudaGraphExec_t exec; cudaEvent_t done; };
+    std::vector<Retired> retired;
+    void reap() {
+        size_t keep = 0;
+        for (size_t k = 0; k < retired.size(); ++k) {
+            if (cudaEventQuery(retired[k].done) == cudaSuccess) {
+                cudaGraphExecDestroy(retired[k].exec);
+                cudaEventDestroy(retired[k].done);
+            } else {
+                retired[keep++] = retired[k];
+            }
+        }
+        retired.resize(keep);
+        cudaGetLastError();   // cudaErrorNotReady from the query is not an error
+    }
+    // make `exec` an executable of `graph`: update in place when the topology allows it
+    cudaError_t adopt(cudaGraph_t graph) {
+        if (exec) {
+            cudaGraphExecUpdateResultInfo info;
+            if (cudaGraphExecUpdate(exec, graph, &info) == cudaSuccess) return cudaSuccess;
+            cudaGetLastError();
+            cudaEvent_t done = nullptr;
+            if (cudaEventCreateWithFlags(&done, cudaEventDisableTiming) == cudaSuccess &&
+                cudaEventRecord(done, stream) == cudaSuccess)
+                retired.push_back({exec, done});
+            exec = nullptr;   // (if the event could not be made the old executable is leaked, not freed early)
+        }
+        return cudaGraphInstantiate(&exec, graph, 0);
+    }
+};
+static std::atomic<int> g_render_graphs{1};
+// merl_render's workspace comes from a private stream-ordered pool that keeps its memory between
+// calls (release threshold = max): the default pool hands freed memory back to the OS at the next
+// synchronisation, which made every call pay milliseconds for a fresh 0.5-4 GB mapping.
+static cudaMemPool_t render_pool(int device) {
+    static std::mutex mu;
+    static cudaMemPool_t pools[64] = {};
+    if (device < 0 || device >= 64) return nullptr;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!pools[device]) {
+        cudaMemPoolProps props{};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        cudaMemPool_t pool = nullptr;
+        if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        uint64_t keep = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        pools[device] = pool;
+    }
+    return pools[device];
+}
+static RenderSide* render_side(int device) {
+    static std::mutex mu;
+    static RenderSide* sides[64] = {};
+    if (device < 0 || device >= 64) { fail(MERL_ERR_ARG, "device %d out of range", device); return nullptr; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!sides[device]) {
+        RenderSide* r = new RenderSide();
+        if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r->fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r->join, cudaEventDisableTiming) != cudaSuccess) {
+            fail(MERL_ERR_CUDA, "cannot create the render side stream: %s", cudaGetErrorString(cudaGetLastError()));
+            delete r;
+            return nullptr;
+        }
+        sides[device] = r;
+    }
+    return sides[device];
+}
+extern "C" int merl_set_render_graphs(int on) {
+    g_render_graphs.store(on ? 1 : 0);
+    return MERL_OK;
+}
+
 extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres, int nspheres,
                            const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out,
                            merl_stream_t stream_) {
@@ -1050,7 +1143,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     const int64_t npix = (int64_t)p->width * p->height;
     const int64_t total = npix * (p->spp_end - p->spp_begin);
     if (total == 0) { if (stats_out) memset(stats_out, 0, sizeof *stats_out); return MERL_OK; }
-    int64_t cap = p->wavefront > 0 ? p->wavefront : (1 << 21);
+    int64_t cap = p->wavefront > 0 ? p->wavefront : (1 << 23);   // 8 Mi paths: 2 GB of workspace, kept in the pool
     if (cap > total) cap = total;
     cap = (cap + 255) & ~(int64_t)255;
 
@@ -1058,8 +1151,10 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     const size_t nf = 19, ni = 4;
     size_t bytes = cap * (nf * 4 + ni * 4) + cap * 16 * 9 + 256;
     bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(4 * ntables + 4) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
+    bytes += (size_t)cap * 4 * 2 + 512 + 256 + (size_t)kMaxClusters * 16 + 256 + 256;   // live lists, their counters, clusters, pass info
     char* ws = nullptr;
-    CUDA_TRY(cudaMallocAsync(&ws, bytes, s));
+    if (cudaMemPool_t pool = render_pool(t0->device)) CUDA_TRY(cudaMallocFromPoolAsync((void**)&ws, bytes, pool, s));
+    else CUDA_TRY(cudaMallocAsync(&ws, bytes, s));
     char* cur = ws;
     auto take = [&](size_t b) { char* r = cur; cur += (b + 255) & ~(size_t)255; return r; };
     float4* f4 = reinterpret_cast<float4*>(take(cap * 16 * 9));
@@ -1076,12 +1171,55 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     int *d_seg = d_counts + ntables, *d_cursor = d_seg + ntables + 1, *d_items = d_cursor + ntables;
     TableDev* d_tabs = reinterpret_cast<TableDev*>(take(sizeof(TableDev) * ntables));
     unsigned long long* d_nq = reinterpret_cast<unsigned long long*>(take(8));
+    int* d_live[2] = {reinterpret_cast<int*>(take((size_t)cap * 4)), reinterpret_cast<int*>(take((size_t)cap * 4))};
+    int* d_nlive = reinterpret_cast<int*>(take(2 * 4));
+    float4* d_clus = reinterpret_cast<float4*>(take((size_t)kMaxClusters * 16));
+    PassInfo* d_pass = reinterpret_cast<PassInfo*>(take(sizeof(PassInfo)));
 
-    std::vector<float4> hs(nspheres);
+    // Spheres along a Morton curve, kClusterSize consecutive ones under one bounding sphere
+    // (merl_render.cuh: intersect_spheres).  The device only ever uses the sorted order.
+    std::vector<float4> hs(nspheres), hc((nspheres + kClusterSize - 1) / kClusterSize);
     std::vector<int> hm(nspheres);
-    for (int k = 0; k < nspheres; ++k) {
-        hs[k] = make_float4(spheres[k].cx, spheres[k].cy, spheres[k].cz, spheres[k].radius);
-        hm[k] = spheres[k].material;
+    {
+        float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+        for (int k = 0; k < nspheres; ++k) {
+            const float c[3] = {spheres[k].cx, spheres[k].cy, spheres[k].cz};
+            for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], c[a]); hi[a] = std::max(hi[a], c[a]); }
+        }
+        auto spread = [](uint32_t v) {   // 10 bits -> every third bit
+            v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu;
+            v = (v | (v << 4)) & 0x030C30C3u; v = (v | (v << 2)) & 0x09249249u;
+            return v;
+        };
+        std::vector<std::pair<uint32_t, int>> order(nspheres);
+        for (int k = 0; k < nspheres; ++k) {
+            const float c[3] = {spheres[k].cx, spheres[k].cy, spheres[k].cz};
+            uint32_t code = 0;
+            for (int a = 0; a < 3; ++a) {
+                const float ext = hi[a] - lo[a];
+                const uint32_t q = ext > 0.f ? (uint32_t)std::min(1023.f, (c[a] - lo[a]) / ext * 1023.f) : 0u;
+                code |= spread(q) << a;
+            }
+            order[k] = {code, k};
+        }
+        std::sort(order.begin(), order.end());
+        for (int k = 0; k < nspheres; ++k) {
+            const merl_sphere_t& sp = spheres[order[k].second];
+            hs[k] = make_float4(sp.cx, sp.cy, sp.cz, sp.radius);
+            hm[k] = sp.material;
+        }
+        for (size_t g = 0; g < hc.size(); ++g) {
+            const int s0 = (int)g * kClusterSize, s1 = std::min(s0 + kClusterSize, nspheres);
+            double c[3] = {0, 0, 0};
+            for (int k = s0; k < s1; ++k) { c[0] += hs[k].x; c[1] += hs[k].y; c[2] += hs[k].z; }
+            for (int a = 0; a < 3; ++a) c[a] /= (s1 - s0);
+            double r = 0;
+            for (int k = s0; k < s1; ++k) {
+                const double dx = hs[k].x - c[0], dy = hs[k].y - c[1], dz = hs[k].z - c[2];
+                r = std::max(r, std::sqrt(dx * dx + dy * dy + dz * dz) + (double)hs[k].w);
+            }
+            hc[g] = make_float4((float)c[0], (float)c[1], (float)c[2], (float)(r * (1.0 + 1e-4) + 1e-5));   // conservative
+        }
     }
     std::vector<TableDev> ht(ntables);
     int img_floats_eval = 0, img_floats_full = 0;
@@ -1092,8 +1230,8 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     }
     const int img_e = (int)(((size_t)img_floats_eval * 4 + 127) & ~(size_t)127);
     const int img_f = (int)(((size_t)img_floats_full * 4 + 127) & ~(size_t)127);
-    const int grid_e = t0->num_sms * blocks_per_sm(stream_multi_kernel<EvalPdfAosOp, 4>, (size_t)img_e + kQueueBytes);
-    const int grid_f = t0->num_sms * blocks_per_sm(stream_multi_kernel<SampleAosOp, 3>, (size_t)img_f + kQueueBytes);
+    const int grid_e = t0->num_sms * blocks_per_sm(stream_multi_kernel<EvalPdfAosOp, 4 * kMinbScale>, (size_t)img_e + kQueueBytes);
+    const int grid_f = t0->num_sms * blocks_per_sm(stream_multi_kernel<SampleAosOp, 3 * kMinbScale>, (size_t)img_f + kQueueBytes);
     int rc = MERL_OK;
     int64_t launches = 0;
 #define RT_TRY(x)                                                                                  \
@@ -1107,33 +1245,78 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     {
     RT_TRY(cudaMemcpyAsync(d_sph, hs.data(), sizeof(float4) * nspheres, cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemcpyAsync(d_smat, hm.data(), sizeof(int) * nspheres, cudaMemcpyHostToDevice, s));
+    RT_TRY(cudaMemcpyAsync(d_clus, hc.data(), sizeof(float4) * hc.size(), cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemcpyAsync(d_tabs, ht.data(), sizeof(TableDev) * ntables, cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int) * ntables, s));
     RT_TRY(cudaMemsetAsync(d_nq, 0, 8, s));
     float4* film = reinterpret_cast<float4*>(film4);
-    for (int64_t first = 0; first < total; first += cap) {
-        const int np = (int)std::min<int64_t>(cap, total - first);
-        const int nb = (np + 255) / 256;
-        rt_raygen_kernel<<<nb, 256, 0, s>>>(R, P, first, np);
-        ++launches;
+    const PassInfo pass0{0, (int)std::min<int64_t>(cap, total), 0};
+    RT_TRY(cudaMemcpyAsync(d_pass, &pass0, sizeof pass0, cudaMemcpyHostToDevice, s));
+    const int64_t npasses = (total + cap - 1) / cap;
+    const int nb = (int)((cap + 255) / 256);
+    // One wavefront pass = 2 + 7 max_depth launches, most of them over a handful of live paths at
+    // the later bounces: launch-latency bound when enqueued one by one.  The pass is recorded once
+    // as a CUDA graph (it reads its sample range from d_pass, advanced by its last node) and
+    // replayed npasses times.  Capture needs a non-legacy stream, so the work runs on a side
+    // stream that is forked from and joined back into the caller's stream with events: the call
+    // stays asynchronous and ordered on `stream`.
+    auto enqueue_pass = [&](cudaStream_t q) {
+        rt_raygen_kernel<<<nb, 256, 0, q>>>(R, P, d_pass);
+        // from depth 1 on the kernels walk the live list (grid-stride over a grid that covers a few
+        // waves; CTAs beyond the live count exit at once)
+        const int nbl = std::min(nb, t0->num_sms * 16);
         for (int depth = 0; depth <= p->max_depth; ++depth) {
-            rt_trace_kernel<<<nb, 256, 0, s>>>(R, P, A, d_sph, d_smat, np, depth, film, d_nq);
-            ++launches;
+            const int cur = depth & 1, nxt = cur ^ 1;
+            const LiveList L{depth ? d_live[cur] : nullptr, d_nlive + cur, d_live[nxt], d_nlive + nxt};
+            const int g = depth ? nbl : nb;
+            rt_trace_kernel<<<g, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, d_nq, L);
             if (depth == p->max_depth) break;   // the last trace only collects escaped paths
             // live queries -> contiguous, material-sorted segments (with one table this is plain
             // stream compaction: the BSDF stage then touches live queries only)
-            rt_hist_kernel<<<std::min(nb, t0->num_sms * 4), 256, sizeof(int) * ntables, s>>>(P.mat, np, ntables, d_counts);
-            rt_scan_kernel<<<1, 1024, 0, s>>>(d_counts, ntables, d_seg, d_cursor, d_items, 4 * std::min(grid_e, grid_f));
-            rt_scatter_kernel<<<nb, 256, 0, s>>>(P, A, B, np, d_cursor);
-            stream_multi_kernel<EvalPdfAosOp, 4><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, s>>>(
+            rt_hist_kernel<<<std::min(g, t0->num_sms * 4), 256, sizeof(int) * ntables, q>>>(P.mat, d_pass, ntables, d_counts, L);
+            rt_scan_kernel<<<1, 1024, 0, q>>>(d_counts, ntables, d_seg, d_cursor, d_items, 4 * std::min(grid_e, grid_f),
+                                              d_nlive + nxt);
+            rt_scatter_kernel<<<g, 256, 0, q>>>(P, A, B, d_pass, d_cursor, L);
+            stream_multi_kernel<EvalPdfAosOp, 4 * kMinbScale><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, q>>>(
                 d_tabs, ntables, d_seg, d_items, EvalPdfAosOp{B.wi4, B.woe4, B.fe4}, img_e);
-            stream_multi_kernel<SampleAosOp, 3><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, s>>>(
+            stream_multi_kernel<SampleAosOp, 3 * kMinbScale><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, q>>>(
                 d_tabs, ntables, d_seg, d_items, SampleAosOp{B.wi4, B.u4, B.wos4, B.w4}, img_f);
-            rt_shade_kernel<<<nb, 256, 0, s>>>(R, P, B, np, film);
-            launches += 6;
+            rt_shade_kernel<<<g, 256, 0, q>>>(R, P, B, d_seg + ntables, film, L);
         }
+        rt_advance_kernel<<<1, 1, 0, q>>>(d_pass, (long long)total, (int)cap);
+    };
+    const int64_t per_pass = 3 + 7 * (int64_t)p->max_depth;
+    if (npasses >= 2 && g_render_graphs.load()) {
+        RenderSide* side = render_side(t0->device);
+        if (!side) { rc = MERL_ERR_CUDA; goto done; }
+        std::lock_guard<std::mutex> lk(side->mu);
+        side->reap();
+        RT_TRY(cudaEventRecord(side->fork, s));
+        RT_TRY(cudaStreamWaitEvent(side->stream, side->fork, 0));
+        cudaGraph_t graph = nullptr;
+        RT_TRY(cudaStreamBeginCapture(side->stream, cudaStreamCaptureModeThreadLocal));
+        enqueue_pass(side->stream);
+        {
+            const cudaError_t ec = cudaStreamEndCapture(side->stream, &graph);
+            if (ec != cudaSuccess || !graph) {
+                rc = fail(MERL_ERR_CUDA, "graph capture of a render pass failed: %s", cudaGetErrorString(ec));
+                goto done;
+            }
+            const cudaError_t ei = side->adopt(graph);
+            cudaGraphDestroy(graph);
+            if (ei != cudaSuccess) {
+                rc = fail(MERL_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ei));
+                goto done;
+            }
+        }
+        for (int64_t k = 0; k < npasses; ++k) RT_TRY(cudaGraphLaunch(side->exec, side->stream));
+        RT_TRY(cudaEventRecord(side->join, side->stream));
+        RT_TRY(cudaStreamWaitEvent(s, side->join, 0));
+    } else {
+        for (int64_t k = 0; k < npasses; ++k) enqueue_pass(s);
         RT_TRY(cudaGetLastError());
     }
+    launches = npasses * per_pass;
     g_launches.fetch_add(launches);
     if (stats_out) {
         unsigned long long nq = 0;

@@ -63,7 +63,10 @@ template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p,
 // for every input, including adversarial batches in which every query is uncertain (the warp
 // then flushes every iteration: slow, still exact).  No scratch memory, no second launch.
 // ------------------------------------------------------------------------------------------
-constexpr int kThreadsPerCta = 256;
+#ifndef MERL_CTA_THREADS
+#define MERL_CTA_THREADS 256
+#endif
+constexpr int kThreadsPerCta = MERL_CTA_THREADS;
 constexpr int kWarpsPerCta = kThreadsPerCta / 32;
 constexpr int kQueueCap = 256;                      // entries per warp (8 B each)
 constexpr int kQueueBytes = kWarpsPerCta * (kQueueCap * 8 + 8);
@@ -243,16 +246,22 @@ struct QueryOp {
 // ------------------------------------------------------------------------------------------
 // sample   (row A6; oracle: draw_direction + eval_pdf_one)
 // ------------------------------------------------------------------------------------------
-// Largest i in [0, nh-1] with row[i] <= u (row[0] = 0).  Per-lane, fixed trip count (no
-// divergence): descending power-of-two strides over the smem-resident row.
-__device__ __forceinline__ int search_lane(const float* row, int nh, int step0, float u) {
-    int lo = 0;
-    for (int step = step0; step > 0; step >>= 1) {
-        const int m = lo + step;
-        const float e = row[min(m, nh - 1)];
-        lo = (m < nh && e <= u) ? m : lo;
+// Largest i in [0, nh-1] with row[i] <= u (row[0] = 0).  Per-lane bisection over the smem-resident
+// row with compile-time strides (kMaxNH = 256 -> 8 steps, fully unrolled, no branches): the running
+// pointer makes each step one LDS with an immediate offset, one bound test, one compare and one
+// predicated add.  A probe past the row's end is rejected by the bound test before its value is
+// used; it still reads shared memory, at most 128 floats past the row, which stays inside the CTA's
+// allocation because the redo queues (kQueueBytes >= 512) follow the table image.
+__device__ __forceinline__ int search_lane(const float* row, int nh, int /*step0*/, float u) {
+    static_assert(kMaxNH <= 256 && kQueueBytes >= 512, "search_lane: 8 strides, probes may overrun by 128 floats");
+    const float* p = row;
+    const float* const end = row + nh;
+#pragma unroll
+    for (int S = 128; S > 0; S >>= 1) {
+        const float e = p[S];
+        p = (p + S < end && e <= u) ? p + S : p;
     }
-    return lo;
+    return (int)(p - row);
 }
 // Same result, warp-cooperative: the warp walks its queries; for each, every lane tests a
 // strided share of the row (conflict-free LDS) and __ballot_sync/__popc count the entries <= u.
@@ -304,7 +313,7 @@ __device__ __forceinline__ void draw_direction(const SmemView& v, const float* r
     // shared transcendental work
     float sn, cs;
     sincospif(spec ? 2.f * uy : ph, &sn, &cs);
-    const float root = sqrtf(spec ? m * (2.f - m) : fmaxf(0.f, (1.f - ar) * (1.f + ar)));
+    const float root = sqrt_approx(spec ? m * (2.f - m) : fmaxf(0.f, (1.f - ar) * (1.f + ar)));   // 1 ulp
     const float rad = spec ? root : r;
     const float px = rad * cs, py = rad * sn, pz = spec ? 1.f - m : root;   // cosine: wo; tabulated: h
     const float c2 = 2.f * fmaf(ax, px, fmaf(ay, py, az * pz));

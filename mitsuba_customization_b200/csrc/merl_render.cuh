@@ -57,7 +57,7 @@ struct PathState {
     float *hx, *hy, *hz;                      // hit point
     int* pixel;                               // -1 = dead
     int* sample;
-    int* slot;                                // position of this path's query in the (sorted) stage buffers
+    int* slot;                                // indexed by stage slot: the path whose query sits in that slot
     int* mat;                                 // material at the current hit, -1 when the path has no query this bounce
 };
 
@@ -68,39 +68,67 @@ __device__ __forceinline__ void film_add(float4* film, int pixel, float r, float
     red_add_v4(film + pixel, r, g, b, w);
 }
 
+// Two-level intersection.  The host sorts the spheres along a Morton curve and groups kClusterSize
+// consecutive ones under a bounding sphere (merl_render); a ray tests the bound first and skips the
+// group when it misses it, when the bound lies behind the origin, or when it starts beyond the best
+// hit so far.  The per-sphere arithmetic is the brute-force loop's (and the oracle's), so the nearest
+// hit is the same one; only exact ties in t could resolve to another sphere.
+constexpr int kClusterSize = 8;
+constexpr int kMaxClusters = kMaxSpheres / kClusterSize;
+
+// ray vs bounding sphere: false = no sphere inside can be hit in (kRayEps, t_max)
+__device__ __forceinline__ bool cluster_may_hit(const float4 c, float ox, float oy, float oz, float dx, float dy,
+                                                float dz, float t_max) {
+    const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
+    const float b = lx * dx + ly * dy + lz * dz;
+    const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
+    const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
+    if (disc < 0.f) return false;
+    const float sq = sqrtf(disc);
+    return (-b + sq >= kRayEps) && (-b - sq <= t_max);
+}
+
 // nearest hit of (o, d) with the spheres in shared memory; returns sphere index or -1
-__device__ __forceinline__ int intersect_spheres(const float4* sph, int n, float ox, float oy, float oz, float dx,
-                                                 float dy, float dz, float& t_hit) {
+__device__ __forceinline__ int intersect_spheres(const float4* sph, const float4* clus, int n, float ox, float oy,
+                                                 float oz, float dx, float dy, float dz, float& t_hit) {
     int best = -1;
     float tb = 3.0e38f;
-    for (int s = 0; s < n; ++s) {
-        const float4 c = sph[s];
-        const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
-        const float b = lx * dx + ly * dy + lz * dz;
-        // discriminant from the rejection of l on d (|l - b d|^2), not b^2 - (|l|^2 - r^2): the latter
-        // cancels catastrophically in fp32 when the origin is many radii away (Ray Tracing Gems ch. 7)
-        const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
-        const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
-        if (disc < 0.f) continue;
-        const float sq = sqrtf(disc);
-        float t = -b - sq;
-        if (t < kRayEps) t = -b + sq;
-        if (t >= kRayEps && t < tb) { tb = t; best = s; }
+    for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize) {
+        if (!cluster_may_hit(clus[k], ox, oy, oz, dx, dy, dz, tb)) continue;
+        const int s1 = min(s0 + kClusterSize, n);
+        for (int s = s0; s < s1; ++s) {
+            const float4 c = sph[s];
+            const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
+            const float b = lx * dx + ly * dy + lz * dz;
+            // discriminant from the rejection of l on d (|l - b d|^2), not b^2 - (|l|^2 - r^2): the latter
+            // cancels catastrophically in fp32 when the origin is many radii away (Ray Tracing Gems ch. 7)
+            const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
+            const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
+            if (disc < 0.f) continue;
+            const float sq = sqrtf(disc);
+            float t = -b - sq;
+            if (t < kRayEps) t = -b + sq;
+            if (t >= kRayEps && t < tb) { tb = t; best = s; }
+        }
     }
     t_hit = tb;
     return best;
 }
-__device__ __forceinline__ bool occluded(const float4* sph, int n, float ox, float oy, float oz, float dx, float dy,
-                                         float dz) {
-    for (int s = 0; s < n; ++s) {
-        const float4 c = sph[s];
-        const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
-        const float b = lx * dx + ly * dy + lz * dz;
-        const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
-        const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
-        if (disc < 0.f) continue;
-        const float sq = sqrtf(disc);
-        if (-b - sq >= kRayEps || -b + sq >= kRayEps) return true;
+__device__ __forceinline__ bool occluded(const float4* sph, const float4* clus, int n, float ox, float oy, float oz,
+                                         float dx, float dy, float dz) {
+    for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize) {
+        if (!cluster_may_hit(clus[k], ox, oy, oz, dx, dy, dz, 3.0e38f)) continue;
+        const int s1 = min(s0 + kClusterSize, n);
+        for (int s = s0; s < s1; ++s) {
+            const float4 c = sph[s];
+            const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
+            const float b = lx * dx + ly * dy + lz * dz;
+            const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
+            const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
+            if (disc < 0.f) continue;
+            const float sq = sqrtf(disc);
+            if (-b - sq >= kRayEps || -b + sq >= kRayEps) return true;
+        }
     }
     return false;
 }
@@ -119,10 +147,25 @@ __device__ __forceinline__ float power_heuristic(float a, float b) {
 }
 
 // ---- ray generation: path i of the pass <-> global sample (first + i) ----------------------------
-__global__ void rt_raygen_kernel(const RenderDev R, const PathState P, const int64_t first, const int npaths) {
+// Which slice of the render's samples the current wavefront pass covers.  It lives in device memory
+// and is advanced by rt_advance_kernel at the end of a pass, so that one captured CUDA graph of a
+// pass can be replayed for every pass of a render (merl_render).
+struct PassInfo {
+    long long first;   // global sample index of the pass's path 0
+    int np;            // paths in this pass (<= cap)
+    int pad;
+};
+__global__ void rt_advance_kernel(PassInfo* pass, const long long total, const int cap) {
+    const long long first = pass->first + cap;
+    const long long left = total - first;
+    pass->first = first;
+    pass->np = left >= cap ? cap : (left > 0 ? (int)left : 0);
+}
+
+__global__ void rt_raygen_kernel(const RenderDev R, const PathState P, const PassInfo* __restrict__ pass) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npaths) return;
-    const int64_t gid = first + i;
+    if (i >= pass->np) return;
+    const int64_t gid = pass->first + i;
     const int npix = R.width * R.height;
     const int pixel = (int)(gid % npix), s = R.spp_begin + (int)(gid / npix);
     uint32_t rnd[4];
@@ -139,7 +182,7 @@ __global__ void rt_raygen_kernel(const RenderDev R, const PathState P, const int
     P.lr[i] = 0.f; P.lg[i] = 0.f; P.lb[i] = 0.f;
     P.prev_pdf[i] = 0.f;
     P.pixel[i] = pixel; P.sample[i] = s;
-    P.mat[i] = -1; P.slot[i] = i;
+    P.mat[i] = -1;
 }
 
 // BSDF-stage buffers of one pass (float4 AoS over `cap` slots)
@@ -149,23 +192,25 @@ struct StageBuf {
 };
 
 // ---- trace: intersect, terminate misses, prepare the BSDF-stage inputs ---------------------------
-__global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const PathState P, const StageBuf S,
-                                                       const float4* __restrict__ spheres,
-                                                       const int* __restrict__ sphere_mat, const int npaths,
-                                                       const int depth, float4* __restrict__ film,
-                                                       unsigned long long* __restrict__ nquery) {
-    __shared__ float4 sph[kMaxSpheres];
-    __shared__ int smat[kMaxSpheres];
-    for (int s = threadIdx.x; s < R.nspheres; s += blockDim.x) { sph[s] = spheres[s]; smat[s] = sphere_mat[s]; }
-    __syncthreads();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npaths) return;
+// Live paths.  Depth 0 walks the pass's paths directly; from depth 1 on the kernels walk the list of
+// paths that the previous bounce's shade kernel continued (live_in[0 .. *nlive_in)), so every
+// per-bounce kernel costs in proportion to the paths still alive, not to the pass size.
+struct LiveList {
+    const int* in;         // NULL at depth 0
+    const int* count_in;
+    int* out;              // written by rt_shade_kernel
+    int* count_out;        // zeroed by rt_scan_kernel of the same bounce
+};
+
+__device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
+                                          const float4* clus, const int* smat, const int i, const int depth,
+                                          float4* __restrict__ film, unsigned long long* __restrict__ nquery) {
     const int pixel = P.pixel[i];
     const float4 dead = make_float4(0.f, 0.f, -1.f, 0.f);
     if (pixel < 0) { P.mat[i] = -1; S.wi4[i] = dead; S.woe4[i] = dead; return; }
     const float ox = P.ox[i], oy = P.oy[i], oz = P.oz[i], dx = P.dx[i], dy = P.dy[i], dz = P.dz[i];
     float t;
-    const int hit = intersect_spheres(sph, R.nspheres, ox, oy, oz, dx, dy, dz, t);
+    const int hit = intersect_spheres(sph, clus, R.nspheres, ox, oy, oz, dx, dy, dz, t);
     bool finish = false;
     float lr = P.lr[i], lg = P.lg[i], lb = P.lb[i];
     if (hit < 0) {
@@ -207,7 +252,7 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
     const float ex = er * ec, ey = er * es;
     float4 woe = dead;
     const float lz = ex * nx + ey * ny + ez * nz;
-    if (lz > 0.f && !occluded(sph, R.nspheres, fmaf(kRayEps, nx, hx), fmaf(kRayEps, ny, hy), fmaf(kRayEps, nz, hz), ex, ey, ez))
+    if (lz > 0.f && !occluded(sph, clus, R.nspheres, fmaf(kRayEps, nx, hx), fmaf(kRayEps, ny, hy), fmaf(kRayEps, nz, hz), ex, ey, ez))
         woe = make_float4(ex * s[0] + ey * s[1] + ez * s[2], ex * tt[0] + ey * tt[1] + ez * tt[2], lz, 0.f);
     const int m = smat[hit];
     {   // one counter update per warp: live BSDF queries of this bounce
@@ -216,19 +261,41 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
     }
     P.lr[i] = lr; P.lg[i] = lg; P.lb[i] = lb;
     P.nx[i] = nx; P.ny[i] = ny; P.nz[i] = nz; P.hx[i] = hx; P.hy[i] = hy; P.hz[i] = hz;
-    P.mat[i] = m; P.slot[i] = i;
+    P.mat[i] = m;
     S.wi4[i] = make_float4(wix, wiy, wiz, (float)m);
     S.woe4[i] = woe;
     S.u4[i] = make_float4(u01(rb[0]), u01(rb[1]), u01(rb[2]), 0.f);
 }
 
+__global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const PathState P, const StageBuf S,
+                                                       const float4* __restrict__ spheres,
+                                                       const float4* __restrict__ clusters,
+                                                       const int* __restrict__ sphere_mat,
+                                                       const PassInfo* __restrict__ pass, const int depth,
+                                                       float4* __restrict__ film,
+                                                       unsigned long long* __restrict__ nquery, const LiveList L) {
+    __shared__ float4 sph[kMaxSpheres];
+    __shared__ float4 clus[kMaxClusters];
+    __shared__ int smat[kMaxSpheres];
+    const int count = L.in ? *L.count_in : pass->np;
+    if (blockIdx.x * blockDim.x >= count) return;          // whole CTA beyond the live range
+    for (int s = threadIdx.x; s < R.nspheres; s += blockDim.x) { sph[s] = spheres[s]; smat[s] = sphere_mat[s]; }
+    for (int k = threadIdx.x; k * kClusterSize < R.nspheres; k += blockDim.x) clus[k] = clusters[k];
+    __syncthreads();
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x)
+        trace_one(R, P, S, sph, clus, smat, L.in ? L.in[j] : j, depth, film, nquery);
+}
+
 // ---- counting sort of the live queries by material (multi-material scenes) -----------------------
-__global__ void rt_hist_kernel(const int* __restrict__ mat, const int npaths, const int ntables, int* counts) {
+__global__ void rt_hist_kernel(const int* __restrict__ mat, const PassInfo* __restrict__ pass, const int ntables,
+                               int* counts, const LiveList L) {
     extern __shared__ int h[];
+    const int count = L.in ? *L.count_in : pass->np;
+    if (blockIdx.x * blockDim.x >= count) return;
     for (int k = threadIdx.x; k < ntables; k += blockDim.x) h[k] = 0;
     __syncthreads();
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npaths; i += gridDim.x * blockDim.x) {
-        const int m = mat[i];
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
+        const int m = mat[L.in ? L.in[j] : j];
         if (m >= 0) atomicAdd(&h[m], 1);
     }
     __syncthreads();
@@ -243,10 +310,11 @@ __global__ void rt_hist_kernel(const int* __restrict__ mat, const int npaths, co
 // few items and thin ones (late bounces) still spread over many CTAs instead of one CTA walking
 // many tables.
 __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int ntables, int* seg_off, int* cursor,
-                                                       int* item_off, const int target_items) {
+                                                       int* item_off, const int target_items, int* next_live_count) {
     __shared__ int sc[1024];
     __shared__ int chunk_s;
     const int k = threadIdx.x;
+    if (k == 0) *next_live_count = 0;   // this bounce's shade kernel appends the continuing paths
     const int c = k < ntables ? counts[k] : 0;
     auto scan = [&](int v) {
         sc[k] = v;
@@ -275,28 +343,60 @@ __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int nt
     if (k < ntables) item_off[k] = iinc - items;
     if (k == ntables - 1) { item_off[ntables] = iinc; item_off[ntables + 1] = chunk; }
 }
-__global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B, const int npaths, int* cursor) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B,
+                                  const PassInfo* __restrict__ pass, int* cursor, const LiveList L) {
+    const int count = L.in ? *L.count_in : pass->np;
     const int lane = threadIdx.x & 31;
-    const int m = i < npaths ? P.mat[i] : -1;
-    // one atomic per (warp, material): neighbouring pixels mostly share a material
-    const unsigned peers = __match_any_sync(0xffffffffu, m);
-    int base = 0;
-    const int leader = __ffs(peers) - 1;
-    if (m >= 0 && lane == leader) base = atomicAdd(&cursor[m], __popc(peers));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (m < 0) return;
-    const int slot = base + __popc(peers & ((1u << lane) - 1u));
-    P.slot[i] = slot;
-    B.wi4[slot] = A.wi4[i]; B.woe4[slot] = A.woe4[i]; B.u4[slot] = A.u4[i];
+    // warp-uniform trip count: __match_any_sync needs the whole warp
+    for (int j0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); j0 < count; j0 += gridDim.x * blockDim.x) {
+        const int j = j0 + lane;
+        const int i = j < count ? (L.in ? L.in[j] : j) : -1;
+        const int m = i >= 0 ? P.mat[i] : -1;
+        // one atomic per (warp, material): neighbouring pixels mostly share a material
+        const unsigned peers = __match_any_sync(0xffffffffu, m);
+        int base = 0;
+        const int leader = __ffs(peers) - 1;
+        if (m >= 0 && lane == leader) base = atomicAdd(&cursor[m], __popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (m < 0) continue;
+        const int slot = base + __popc(peers & ((1u << lane) - 1u));
+        P.slot[slot] = i;
+        B.wi4[slot] = A.wi4[i]; B.woe4[slot] = A.woe4[i]; B.u4[slot] = A.u4[i];
+    }
 }
 
 // ---- shade: consume the BSDF-stage outputs, continue or finish the path -------------------------------
+__device__ __forceinline__ bool shade_one(const RenderDev& R, const PathState& P, const StageBuf& S, const int slot,
+                                          const int i, float4* __restrict__ film);
+
+// One thread per BSDF-stage slot (the live queries of this bounce, nq = seg_off[ntables]); paths
+// that continue are appended to the next bounce's live list, one atomic per warp.
 __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const PathState P, const StageBuf S,
-                                                       const int npaths, float4* __restrict__ film) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npaths || P.mat[i] < 0) return;
-    const int slot = P.slot[i];
+                                                       const int* __restrict__ nq_ptr, float4* __restrict__ film,
+                                                       const LiveList L) {
+    const int nq = *nq_ptr;
+    const int lane = threadIdx.x & 31;
+    for (int s0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); s0 < nq; s0 += gridDim.x * blockDim.x) {
+        const int slot = s0 + lane;
+        int i = -1;
+        bool go = false;
+        if (slot < nq) {
+            i = P.slot[slot];
+            go = shade_one(R, P, S, slot, i, film);
+        }
+        const unsigned cont = __ballot_sync(0xffffffffu, go);
+        if (cont) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(L.count_out, __popc(cont));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (go) L.out[base + __popc(cont & ((1u << lane) - 1u))] = i;
+        }
+    }
+}
+
+// true when the path continues with a new ray
+__device__ __forceinline__ bool shade_one(const RenderDev& R, const PathState& P, const StageBuf& S, const int slot,
+                                          const int i, float4* __restrict__ film) {
     const float4 fe = S.fe4[slot], ws = S.wos4[slot], w = S.w4[slot];
     float tr = P.tr[i], tg = P.tg[i], tb = P.tb[i];
     const float mis = power_heuristic(0.0795774715f, fe.w) * 12.5663706f;   // weight / pdf_e
@@ -306,7 +406,7 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
     if (!(ws.w > 0.f) || !(tr + tg + tb > 0.f)) {
         film_add(film, P.pixel[i], lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
         P.pixel[i] = -1; P.mat[i] = -1;
-        return;
+        return false;
     }
     const float nx = P.nx[i], ny = P.ny[i], nz = P.nz[i];
     float s[3], tt[3];
@@ -318,6 +418,7 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
     P.tr[i] = tr; P.tg[i] = tg; P.tb[i] = tb;
     P.lr[i] = lr; P.lg[i] = lg; P.lb[i] = lb;
     P.prev_pdf[i] = ws.w;
+    return true;
 }
 
 // ---- BSDF stage over several tables: work items (one table, <= chunk queries) are dealt to the CTAs
