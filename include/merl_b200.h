@@ -131,7 +131,10 @@ int merl_sample(const merl_table_t* t, const float* wix, const float* wiy, const
                 float* wox, float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb,
                 uint32_t* lobe, merl_stream_t stream);
 /* grad_cells4 (device float4[ncell], caller-zeroed) += d(eval)/d(cells) . (gr, gg, gb).
- * .w accumulates the number of contributing queries.  flags bit0: warp-aggregate equal cells
+ * .w accumulates the number of contributing queries.  Channels of invalid (negative, clamped) cells
+ * receive no gradient: they are kept at zero in grad_cells4 (batches with at least as many queries
+ * as the table has cells scatter unmasked and zero those channels in one pass afterwards, so
+ * grad_cells4 must not be shared with gradients from other sources).  flags bit0: warp-aggregate equal cells
  * with __match_any_sync before the atomic (default on; 0 = plain per-lane RED). */
 #define MERL_BWD_WARP_AGGREGATE 1u
 int merl_backward(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,

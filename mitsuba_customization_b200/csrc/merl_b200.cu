@@ -754,7 +754,7 @@ struct BackwardIn {
     const float *gr, *gg, *gb;
 };
 
-template <int AGG>
+template <int AGG, int GATHER>
 static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* grad, cudaStream_t s) {
     const int fl = t->dev.off_dens;
     const QueryIn& q = in.q;
@@ -763,16 +763,22 @@ static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* g
                      aligned(in.gg, 16) && aligned(in.gb, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        const int rc = launch_op<BackwardOp<4, AGG>, MERL_BWD_MINB>(t, BackwardOp<4, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl,
-                                                        n / 4, s);
+        using Op = BackwardOp<4, AGG, GATHER>;
+        const int rc = launch_op<Op, MERL_BWD_MINB>(t, Op{in.q, in.gr, in.gg, in.gb, grad}, fl, n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;
     }
     if (done < n) {
+        using Op = BackwardOp<1, AGG, GATHER>;
         in.q = offset_in(in.q, done);
         in.gr += done; in.gg += done; in.gb += done;
-        return launch_op<BackwardOp<1, AGG>, 3 * kMinbScale>(t, BackwardOp<1, AGG>{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done,
-                                                s);
+        const int rc = launch_op<Op, 3 * kMinbScale>(t, Op{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done, s);
+        if (rc) return rc;
+    }
+    if (!GATHER && n > 0) {
+        backward_mask_kernel<<<t->num_sms * 8, 256, 0, s>>>(t->d_cells, grad, t->ncell);
+        CUDA_TRY(cudaGetLastError());
+        g_launches.fetch_add(1);
     }
     return MERL_OK;
 }
@@ -788,8 +794,11 @@ extern "C" int merl_backward(const merl_table_t* t, const float* wix, const floa
     DeviceGuard gd(t->device);
     BackwardIn in{{wix, wiy, wiz, wox, woy, woz, active}, gr, gg, gb};
     float4* grad = reinterpret_cast<float4*>(grad_cells4);
-    return (flags & MERL_BWD_WARP_AGGREGATE) ? run_backward<1>(t, in, n, grad, (cudaStream_t)stream)
-                                             : run_backward<0>(t, in, n, grad, (cudaStream_t)stream);
+    // big batches: unmasked scatter + one mask pass over the table; small ones: per-query validity gather
+    const bool gather = n < t->ncell || !t->params.clamp_negative;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (flags & MERL_BWD_WARP_AGGREGATE) return gather ? run_backward<1, 1>(t, in, n, grad, s) : run_backward<1, 0>(t, in, n, grad, s);
+    return gather ? run_backward<0, 1>(t, in, n, grad, s) : run_backward<0, 0>(t, in, n, grad, s);
 }
 
 extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const float* wo4, int64_t n, float* out4,

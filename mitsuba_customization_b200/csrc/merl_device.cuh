@@ -102,6 +102,12 @@ __device__ __forceinline__ float fast_acos01(float x) {
     return sqrt_approx(1.f - x) * p;
 }
 
+// acos(x) on [0,1] given 1 - x computed without cancellation (relative error 2.3e-4 as x -> 1).
+__device__ __forceinline__ float fast_acos01_om(float x, float one_minus_x) {
+    const float p = fmaf(fmaf(fmaf(-0.02087747f, x, 0.07687739f), x, -0.21286782f), x, 1.57075773f);
+    return sqrt_approx(fmaxf(one_minus_x, 0.f)) * p;
+}
+
 struct Bins {
     int ih, id, ip;
 };
@@ -139,7 +145,11 @@ __device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemV
                                                   unsigned& unc, int kc[3]) {
     constexpr float EPS_H = 2e-6f, EPS_D = 2e-6f, EPS_P = 1.5e-6f;  // error budgets: DESIGN.md §3
     // candidates
-    const float th_h = fast_atan2_pos(sqrt_approx(h.rho2), h.sz);
+    // theta_h = acos(sz/|s|) with 1 - cos written as rho^2 / (|s| (|s| + sz)): no cancellation at the
+    // small angles where MERL's sqrt-spaced bins are 2e-4 rad wide (sz > 0 for every valid query;
+    // an invalid one may produce NaN here, which F2I turns into candidate 0)
+    const float ch = __saturatef(h.sz * h.inv_s);
+    const float th_h = fast_acos01_om(ch, h.rho2 * h.inv_s * rcp_approx(h.slen + h.sz));
     const float tq = th_h * t.kh;
     const int kh = min(__float2int_rn(t.theta_h_sqrt ? sqrt_approx(tq) : tq), t.nh);
     const int kd = min(__float2int_rn(fast_acos01(h.A * h.inv_s) * t.kd), t.nd);

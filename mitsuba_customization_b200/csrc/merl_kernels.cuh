@@ -430,7 +430,11 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
                  : "memory");
 }
 
-template <int VEC, int AGG>
+// GATHER = 1: each query reads its cell's validity bits (one more L2 sector per query) and masks
+// its own contribution.  GATHER = 0: contributions are added unmasked and backward_mask_kernel
+// zeroes the channels of invalid cells afterwards in one pass over the table (47 MB of traffic,
+// cheaper than the per-query gather once the batch has more queries than the table has cells).
+template <int VEC, int AGG, int GATHER>
 struct BackwardOp {
     static constexpr int kVec = VEC;
 #ifndef MERL_PF_BACKWARD
@@ -473,7 +477,8 @@ struct BackwardOp {
         }
         float bits[VEC];
 #pragma unroll
-        for (int k = 0; k < VEC; ++k) bits[k] = __ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx[k] + 3]);
+        for (int k = 0; k < VEC; ++k)
+            bits[k] = GATHER ? __ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx[k] + 3]) : 7.f;
 #pragma unroll
         for (int k = 0; k < VEC; ++k) {
             const int m = (int)bits[k];
@@ -517,10 +522,23 @@ struct BackwardOp {
         const HalfDiff h = half_diff_setup(ax, ay, az, bx, by, bz);
         const Bins b = compute_bins(t, v, ax, ay, az, bx, by, bz, h);
         const int idx = flat_index(t, b);
-        const int m = (int)__ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx + 3]);
+        const int m = GATHER ? (int)__ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx + 3]) : 7;
         red_add_v4(grad + idx, (m & 1) ? gr[i] * bz : 0.f, (m & 2) ? gg[i] * bz : 0.f, (m & 4) ? gb[i] * bz : 0.f, 1.f);
     }
 };
+
+// grad[c].rgb *= valid bits of cell c  (invalid channels never receive gradient; see BackwardOp)
+__global__ void backward_mask_kernel(const float4* __restrict__ cells, float4* __restrict__ grad, const int64_t ncell) {
+    for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < ncell; c += (int64_t)gridDim.x * blockDim.x) {
+        const int m = (int)__ldg(&reinterpret_cast<const float*>(cells)[4 * c + 3]);
+        if (m == 7) continue;
+        float4 g = grad[c];
+        if (!(m & 1)) g.x = 0.f;
+        if (!(m & 2)) g.y = 0.f;
+        if (!(m & 4)) g.z = 0.f;
+        grad[c] = g;
+    }
+}
 
 // ------------------------------------------------------------------------------------------
 // AoS variants for the Mitsuba 0.6 wavefront BSDF stage (one float4 per query and buffer)

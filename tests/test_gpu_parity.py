@@ -246,6 +246,37 @@ def test_backward_parity(plug, orc, agg):
     assert float(grad[:, 3].sum()) == float(valid.sum())
 
 
+@pytest.mark.parametrize("agg", [True, False])
+@pytest.mark.parametrize("n", [1 << 18, (1 << 21) + 3])
+def test_backward_masks_invalid_channels(raw_table, agg, n):
+    """A table with invalid (negative) channels scattered through it: those channels get no gradient,
+    both on the small-batch path (per-query validity gather) and on the big-batch path (unmasked
+    scatter + one mask pass over the table; taken when n >= number of cells)."""
+    from mitsuba_customization_b200 import bsdf, synth
+    from oracle import merl_oracle as O
+    raw = raw_table.copy()
+    holes = np.random.default_rng(12).random(raw.shape) < 0.15
+    raw[holes] = -1.0
+    plug = bsdf.MERL(data=raw, device="cuda:0")
+    orc = O.OracleTable(raw, cdf=plug.cdf().cpu().numpy())
+    assert n < plug.info.ncell or n > plug.info.ncell
+    wi, wo = synth.random_queries(n, seed=n)
+    g = np.abs(np.random.default_rng(3).standard_normal((3, n))).astype(np.float32)
+    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), warp_aggregate=agg)
+    ref = orc.backward(wi, wo, g)
+    got = grad.cpu().numpy()
+    _close(got[:, :3], ref[:, :3], "grad with invalid channels")
+    _, _, ref_idx = orc.eval_pdf(wi, wo, want_pdf=False)
+    counts = np.bincount(ref_idx[ref_idx >= 0], minlength=plug.info.ncell)
+    assert np.array_equal(got[:, 3], counts)                          # hit counts are not masked
+    dead = plug.cells().cpu().numpy()[:, 3].astype(int)
+    for c in range(3):
+        assert np.all(got[(dead >> c) & 1 == 0, c] == 0.0)
+    # accumulating a second batch into the same buffer keeps the invariant
+    plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), grad_cells=grad, warp_aggregate=agg)
+    _close(grad.cpu().numpy()[:, :3], 2 * ref[:, :3], "accumulated grad")
+
+
 def test_backward_coherent_batch(plug, orc):
     """Many queries per cell (a coherent wavefront): exercises the warp-aggregation paths.
     An fp32 gradient table (BASELINE.json) accumulates `count` terms per cell with rounding
@@ -359,3 +390,52 @@ def test_merl_file_loader(tmp_path, raw_table):
     synth.write_merl_binary(bad, raw_table[:, :1000], (10, 10, 10))
     with pytest.raises(bsdf.MerlError):
         bsdf.load_dict({"type": "merl", "filename": bad})
+
+
+def test_empty_batch_and_all_inactive(plug):
+    """n = 0 launches nothing and returns empty results; an all-false Mask zeroes every lane."""
+    from mitsuba_customization_b200 import _cabi
+    z3 = torch.empty(3, 0, device="cuda")
+    before = _cabi.launch_count()
+    rgb, pdf = plug.eval_pdf(_ctx(), _si(z3), z3)
+    bs, w = plug.sample(_ctx(), _si(z3), torch.empty(0, device="cuda"), torch.empty(2, 0, device="cuda"))
+    g = plug.backward(_si(z3), z3, z3)
+    assert rgb.shape == (3, 0) and pdf.shape == (0,) and bs.wo.shape == (3, 0) and w.shape == (3, 0)
+    assert _cabi.launch_count() == before and float(g.abs().sum()) == 0.0
+    from mitsuba_customization_b200 import synth
+    wi, wo = synth.random_queries(1001, seed=8)
+    off = torch.zeros(1001, dtype=torch.bool, device="cuda")
+    rgb, pdf = plug.eval_pdf(_ctx(), _si(wi), torch.from_numpy(wo).cuda(), active=off)
+    assert float(rgb.abs().sum()) == 0.0 and float(pdf.abs().sum()) == 0.0
+    g = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.ones(3, 1001, device="cuda"), active=off)
+    assert float(g.abs().sum()) == 0.0
+
+
+def test_non_finite_and_unnormalised_inputs_are_safe(plug, orc):
+    """NaN / inf / zero / huge directions must not fault or index outside the table (they take the
+    redo path); finite unnormalised directions are used as given (assumption B9) and still match."""
+    from mitsuba_customization_b200 import synth
+    n = 4096
+    wi, wo = synth.random_queries(n, seed=77)
+    bad = wi.copy()
+    bad[:, 0::8] = np.nan
+    bad[0, 1::8] = np.inf
+    bad[:, 2::8] = 0.0
+    bad[:, 3::8] *= 1e30
+    ncell = plug.info.ncell
+    idx = plug.bins(_si(bad), torch.from_numpy(wo).cuda()).cpu().numpy()
+    assert ((idx >= -1) & (idx < ncell)).all()
+    rgb, pdf = plug.eval_pdf(_ctx(), _si(bad), torch.from_numpy(wo).cuda())
+    good = np.ones(n, bool)
+    for k in range(4):
+        good[k::8] = False
+    ref_rgb, ref_pdf, ref_idx = orc.eval_pdf(wi, wo)
+    assert np.array_equal(idx[good], ref_idx[good])
+    _close(rgb.cpu().numpy()[:, good], ref_rgb[:, good], "rgb next to non-finite lanes")
+    torch.cuda.synchronize()
+    # unnormalised but finite: same decision as the double oracle on the same (unnormalised) inputs
+    s = np.linspace(0.25, 4.0, n, dtype=np.float32)
+    wi2, wo2 = wi * s, wo * s[::-1]
+    ref = orc.bins(wi2, wo2)
+    got = plug.bins(_si(wi2), torch.from_numpy(np.ascontiguousarray(wo2)).cuda()).cpu().numpy()
+    assert np.array_equal(got[ref["stable"]], ref["idx"][ref["stable"]])
