@@ -8,6 +8,8 @@ file, perturbed by log-normal noise, with below-horizon cells set to -1 as real 
 """
 from __future__ import annotations
 
+import functools
+
 import numpy as np
 
 MERL_DIMS = (90, 90, 180)
@@ -51,14 +53,23 @@ def analytic_brdf(wi, wo, albedo, alpha, f0):
     return np.asarray(albedo)[:, None] / np.pi + spec[None, :]
 
 
+@functools.lru_cache(maxsize=4)
+def _cell_directions(dims, theta_h_sqrt):
+    """(wi, wo) at every cell centre: the same for every table of a layout, so built once."""
+    th, td, pd = bin_centres(dims, theta_h_sqrt)
+    wi, wo = half_diff_to_dirs(th, td, pd)
+    wi.setflags(write=False)
+    wo.setflags(write=False)
+    return wi, wo
+
+
 def synthetic_table(table_id=0, dims=MERL_DIMS, theta_h_sqrt=True, scale=MERL_SCALE, noise=0.1):
     """Raw planar table (3, ncell) float64 in .binary units (value / channel scale)."""
     rng = np.random.Generator(np.random.PCG64(TABLE_SEED + int(table_id)))
     albedo = rng.uniform(0.05, 0.6, size=3)
     alpha = float(rng.uniform(0.05, 0.5))
     f0 = float(rng.uniform(0.02, 0.2))
-    th, td, pd = bin_centres(dims, theta_h_sqrt)
-    wi, wo = half_diff_to_dirs(th, td, pd)
+    wi, wo = _cell_directions(tuple(int(d) for d in dims), bool(theta_h_sqrt))
     f = analytic_brdf(wi, wo, albedo, alpha, f0)
     f = f * np.exp(noise * rng.standard_normal(f.shape))
     raw = f / np.asarray(scale)[:, None]
