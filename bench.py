@@ -300,6 +300,21 @@ def run_b200(args):
         ms_s, _ = timed(lambda: plug.sample(ctx, si, u1, u2), k, 3)
         extras["sample_gquery_s"] = world * n / (ms_s / k * 1e-3) / 1e9
         extras["sample_hbm_gbs_per_gpu"] = 56 * n / (ms_s / k * 1e-3) / 1e9
+        # BASELINE config 3: customized_measurment plugin, 2^24-query eval / sample sweep, L2-resident table
+        cdims = (64, 96, 192)
+        cplug = bsdf.CustomizedMeasurement(data=synth.synthetic_table(7, dims=cdims, theta_h_sqrt=False), resolution=cdims,
+                                           theta_h_mapping="linear", device=f"cuda:{local}")
+        m = min(n, 1 << 24)
+        csi = bsdf.SurfaceInteraction3f(wi=wi[:, :m].contiguous())
+        cwo, cu1, cu2 = wo[:, :m].contiguous(), u1[:m].contiguous(), u2[:, :m].contiguous()
+        cout = torch.empty(4, m, device=dev)
+        ms_ce, _ = timed(lambda: cplug.eval_pdf(ctx, csi, cwo, out=cout), k, 3)
+        ms_cs, _ = timed(lambda: cplug.sample(ctx, csi, cu1, cu2), k, 3)
+        extras["customized_2p24"] = {"resolution": list(cdims), "theta_h_mapping": "linear", "queries_per_gpu": m,
+                                     "table_bytes": int(cplug.info.table_bytes),
+                                     "eval_pdf_gquery_s": world * m / (ms_ce / k * 1e-3) / 1e9,
+                                     "sample_gquery_s": world * m / (ms_cs / k * 1e-3) / 1e9}
+        del cplug, csi, cwo, cu1, cu2, cout
         del u1, u2
         g = torch.randn(3, n, device=dev, generator=gen)
         grad = torch.zeros(plug.info.ncell, 4, device=dev)

@@ -19,6 +19,17 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Debug build (make EXTRA=-DMERL_DEBUG_BOUNDS): device-side asserts on every computed index before it
+// is used -- candidate edges, flat cell index, CDF search result, live-list and stage-slot indices.
+// compute-sanitizer is not available on the measurement pool, so tools/sanitize_run.py is run
+// against this build instead (profiles/r01_bounds_check.txt).
+#ifdef MERL_DEBUG_BOUNDS
+#include <assert.h>
+#define MERL_CHECK(c) assert(c)
+#else
+#define MERL_CHECK(c) ((void)0)
+#endif
+
 namespace merl {
 
 constexpr int kMaxNH = 256, kMaxND = 256, kMaxNP = 512, kMaxNI = 64;
@@ -157,6 +168,7 @@ __device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemV
     float Y = h.slen * fmaf(ay, bx, -ax * by);
     if (Y < 0.f) { X = -X; Y = -Y; }
     const int kp = min(__float2int_rn(fast_atan2_pos(Y, X) * t.kp), t.np);
+    MERL_CHECK(kh >= 0 && kh <= t.nh && kd >= 0 && kd <= t.nd && kp >= 0 && kp <= t.np);
     // one exact-edge comparison per coordinate
     const float eh = v.thr_h[kh], ed = v.thr_d[kd];
     const float2 ep = v.dir_p[kp];

@@ -123,7 +123,11 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
         if (m) {
 #pragma unroll
             for (int q = 0; q < Op::kVec; ++q)
-                if ((m >> q) & 1u) wq.items[atomicAdd(wq.count, 1)] = g * Op::kVec + q;
+                if ((m >> q) & 1u) {
+                    const int at = atomicAdd(wq.count, 1);
+                    MERL_CHECK(at >= 0 && at < kQueueCap);
+                    wq.items[at] = g * Op::kVec + q;
+                }
         }
         __syncwarp();
         if (*reinterpret_cast<volatile int*>(wq.count) > kQueueCap - 32 * Op::kVec) flush_queue(op, t, v, wq, lane);
@@ -140,7 +144,10 @@ __device__ __forceinline__ float pdf_from_bins(const TableDev& t, const SmemView
     const float ps = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
     return h.A > 0.f ? ps : p;
 }
-__device__ __forceinline__ int flat_index(const TableDev& t, const Bins& b) { return (b.ih * t.nd + b.id) * t.np + b.ip; }
+__device__ __forceinline__ int flat_index(const TableDev& t, const Bins& b) {
+    MERL_CHECK(b.ih >= 0 && b.ih < t.nh && b.id >= 0 && b.id < t.nd && b.ip >= 0 && b.ip < t.np);
+    return (b.ih * t.nd + b.id) * t.np + b.ip;
+}
 
 // ------------------------------------------------------------------------------------------
 // bins / eval / pdf / eval_pdf   (rows A1-A5)
@@ -261,6 +268,7 @@ __device__ __forceinline__ int search_lane(const float* row, int nh, int /*step0
         const float e = p[S];
         p = (p + S < end && e <= u) ? p + S : p;
     }
+    MERL_CHECK(p >= row && p < end);
     return (int)(p - row);
 }
 // Same result, warp-cooperative: the warp walks its queries; for each, every lane tests a

@@ -282,8 +282,12 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
     for (int s = threadIdx.x; s < R.nspheres; s += blockDim.x) { sph[s] = spheres[s]; smat[s] = sphere_mat[s]; }
     for (int k = threadIdx.x; k * kClusterSize < R.nspheres; k += blockDim.x) clus[k] = clusters[k];
     __syncthreads();
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x)
-        trace_one(R, P, S, sph, clus, smat, L.in ? L.in[j] : j, depth, film, nquery);
+    MERL_CHECK(count >= 0 && count <= pass->np);
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
+        const int i = L.in ? L.in[j] : j;
+        MERL_CHECK(i >= 0 && i < pass->np);
+        trace_one(R, P, S, sph, clus, smat, i, depth, film, nquery);
+    }
 }
 
 // ---- counting sort of the live queries by material (multi-material scenes) -----------------------
@@ -360,6 +364,7 @@ __global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const Sta
         base = __shfl_sync(0xffffffffu, base, leader);
         if (m < 0) continue;
         const int slot = base + __popc(peers & ((1u << lane) - 1u));
+        MERL_CHECK(slot >= 0 && slot < pass->np && m < 1024);
         P.slot[slot] = i;
         B.wi4[slot] = A.wi4[i]; B.woe4[slot] = A.woe4[i]; B.u4[slot] = A.u4[i];
     }
@@ -382,6 +387,7 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
         bool go = false;
         if (slot < nq) {
             i = P.slot[slot];
+            MERL_CHECK(i >= 0 && P.pixel[i] >= 0 && P.pixel[i] < R.width * R.height);
             go = shade_one(R, P, S, slot, i, film);
         }
         const unsigned cont = __ballot_sync(0xffffffffu, go);
@@ -389,6 +395,7 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
             int base = 0;
             if (lane == 0) base = atomicAdd(L.count_out, __popc(cont));
             base = __shfl_sync(0xffffffffu, base, 0);
+            MERL_CHECK(base >= 0 && base + __popc(cont) <= nq);
             if (go) L.out[base + __popc(cont & ((1u << lane) - 1u))] = i;
         }
     }

@@ -11,6 +11,7 @@ plug = bsdf.MERL(data=synth.synthetic_table(0))
 ctx = bsdf.BSDFContext()
 for n, maker in ((4099, lambda n: synth.random_queries(n, seed=1)), (1 << 14, lambda n: synth.edge_stress_queries(n))):
     wi, wo = maker(n)
+    n = wi.shape[1]
     si, two = bsdf.SurfaceInteraction3f(wi=torch.from_numpy(wi).cuda()), torch.from_numpy(wo).cuda()
     plug.bins(si, two); plug.eval(ctx, si, two); plug.pdf(ctx, si, two); plug.eval_pdf(ctx, si, two)
     u1, u2 = torch.rand(n, device="cuda"), torch.rand(2, n, device="cuda")
