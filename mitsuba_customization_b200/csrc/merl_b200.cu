@@ -719,10 +719,14 @@ static int run_sample(const merl_table* t, SampleIn in, int64_t n, SampleOut out
                      aligned(out.woy, 16) && aligned(out.woz, 16) && aligned(out.pdf, 16) && aligned(out.wr, 16) &&
                      aligned(out.wg, 16) && aligned(out.wb, 16) && aligned(out.lobe, 16);
     int64_t done = 0;
-    if (vec && n >= 4) {
-        const int rc = launch_op<SampleOp<4, SEARCH>, MERL_SAMPLE_MINB>(t, SampleOp<4, SEARCH>{in, out}, fl, n / 4, s);
+#ifndef MERL_SAMPLE_VEC
+#define MERL_SAMPLE_VEC 4
+#endif
+    constexpr int SV = MERL_SAMPLE_VEC;
+    if (vec && n >= SV) {
+        const int rc = launch_op<SampleOp<SV, SEARCH>, MERL_SAMPLE_MINB>(t, SampleOp<SV, SEARCH>{in, out}, fl, n / SV, s);
         if (rc) return rc;
-        done = (n / 4) * 4;
+        done = (n / SV) * SV;
     }
     if (done < n) {
         in.wix += done; in.wiy += done; in.wiz += done; in.u1 += done; in.u2x += done; in.u2y += done;

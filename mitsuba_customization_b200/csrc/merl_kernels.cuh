@@ -28,7 +28,14 @@ template <> __device__ __forceinline__ Pack<4> load_stream<4>(const float* p, in
     const float4 f = __ldcs(reinterpret_cast<const float4*>(p) + g);
     Pack<4> r; r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w; return r;
 }
+template <> __device__ __forceinline__ Pack<2> load_stream<2>(const float* p, int64_t g) {
+    const float2 f = __ldcs(reinterpret_cast<const float2*>(p) + g);
+    Pack<2> r; r.v[0] = f.x; r.v[1] = f.y; return r;
+}
 template <int VEC> __device__ __forceinline__ void store_stream(float* p, int64_t g, const Pack<VEC>& a);
+template <> __device__ __forceinline__ void store_stream<2>(float* p, int64_t g, const Pack<2>& a) {
+    __stcs(reinterpret_cast<float2*>(p) + g, make_float2(a.v[0], a.v[1]));
+}
 template <> __device__ __forceinline__ void store_stream<1>(float* p, int64_t g, const Pack<1>& a) {
     __stcs(p + g, a.v[0]);
 }
@@ -46,6 +53,11 @@ template <int VEC> __device__ __forceinline__ void prefetch_stream(const float* 
 template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
 template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
     return p ? (p[g] != 0) : 1u;
+}
+template <> __device__ __forceinline__ unsigned load_active<2>(const uint8_t* p, int64_t g) {
+    if (!p) return 0x3u;
+    const unsigned w = __ldcs(reinterpret_cast<const unsigned short*>(p) + g);
+    return ((w & 0xFFu) != 0) | ((w >> 8) != 0) << 1;
 }
 template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p, int64_t g) {
     if (!p) return 0xFu;
@@ -407,6 +419,8 @@ struct SampleOp {
             if (VEC == 4) {
                 reinterpret_cast<uint4*>(out.lobe)[g] = make_uint4(lobe[0], lobe[VEC > 1 ? 1 : 0],
                                                                   lobe[VEC > 2 ? 2 : 0], lobe[VEC > 3 ? 3 : 0]);
+            } else if (VEC == 2) {
+                reinterpret_cast<uint2*>(out.lobe)[g] = make_uint2(lobe[0], lobe[VEC > 1 ? 1 : 0]);
             } else {
                 out.lobe[g] = lobe[0];
             }
