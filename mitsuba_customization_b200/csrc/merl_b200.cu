@@ -261,7 +261,8 @@ static inline bool aligned(const void* p, size_t a) { return p == nullptr || ((u
 template <typename Op, int MINB>
 static int launch_op(const merl_table* t, const Op& op, int image_floats, int64_t ngroups, cudaStream_t s) {
     const int img = (int)(((size_t)image_floats * sizeof(float) + 127) & ~(size_t)127);
-    return launch_persistent(t, stream_kernel<Op, MINB>, (size_t)img + kQueueBytes, ngroups, s, t->dev, op, ngroups,
+    const size_t stage = (size_t)Op::kStageVecs * 16 * kThreads;
+    return launch_persistent(t, stream_kernel<Op, MINB>, (size_t)img + kQueueBytes + stage, ngroups, s, t->dev, op, ngroups,
                              img);
 }
 static inline int eval_floats(const merl_table* t, bool pdf) { return pdf ? t->dev.image_eval_floats : t->dev.off_dens; }

@@ -18,6 +18,11 @@ namespace merl {
 // ------------------------------------------------------------------------------------------
 // streamed SoA access: VEC consecutive queries per thread, evict-first transactions
 // ------------------------------------------------------------------------------------------
+#ifndef MERL_CTA_THREADS
+#define MERL_CTA_THREADS 256
+#endif
+constexpr int kThreadsPerCta = MERL_CTA_THREADS;
+
 template <int VEC> struct Pack { float v[VEC]; };
 
 template <int VEC> __device__ __forceinline__ Pack<VEC> load_stream(const float* p, int64_t g);
@@ -50,6 +55,21 @@ template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g,
 template <int VEC> __device__ __forceinline__ void prefetch_stream(const float* p, int64_t g) {
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p + g * VEC));
 }
+// Register-free input staging (ops with kStageVecs > 0): while a lane works on its current group it
+// has an LDGSTS (cp.async, L2-only) in flight that lands the NEXT group's kStageVecs x 16 B in the
+// lane's own shared-memory slot, so the HBM + L2 latency of the streamed inputs is off the critical
+// path without spending registers on a second buffer.  Each lane reads only what it copied itself:
+// no barrier, just cp.async.wait_group.  The slot is re-armed after its contents are in registers.
+__device__ __forceinline__ void cp_async16(float4* smem_dst, const float* gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ Pack<4> load_slot(const float4* slot, int k) {
+    const float4 f = slot[k * kThreadsPerCta];
+    Pack<4> r; r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w; return r;
+}
 template <int VEC> __device__ __forceinline__ unsigned load_active(const uint8_t* p, int64_t g);
 template <> __device__ __forceinline__ unsigned load_active<1>(const uint8_t* p, int64_t g) {
     return p ? (p[g] != 0) : 1u;
@@ -75,10 +95,6 @@ template <> __device__ __forceinline__ unsigned load_active<4>(const uint8_t* p,
 // for every input, including adversarial batches in which every query is uncertain (the warp
 // then flushes every iteration: slow, still exact).  No scratch memory, no second launch.
 // ------------------------------------------------------------------------------------------
-#ifndef MERL_CTA_THREADS
-#define MERL_CTA_THREADS 256
-#endif
-constexpr int kThreadsPerCta = MERL_CTA_THREADS;
 constexpr int kWarpsPerCta = kThreadsPerCta / 32;
 constexpr int kQueueCap = 256;                      // entries per warp (8 B each)
 constexpr int kQueueBytes = kWarpsPerCta * (kQueueCap * 8 + 8);
@@ -108,6 +124,8 @@ __device__ __forceinline__ void flush_queue(const Op& op, const TableDev& t, con
 // Op interface:
 //   static constexpr int kVec       queries per lane and iteration
 //   static constexpr int kPrefetch  L2 prefetch distance in iterations (0 = none); void prefetch(g)
+//   static constexpr int kStageVecs 16-byte vectors per lane staged through shared memory one iteration
+//                                   ahead (0 = none); void stage(slot, g); unsigned hot_staged(...)
 //   int image_floats(t)             floats of the table image the op needs in shared memory
 //   unsigned hot(t, v, g, in_range, lane)   tier-1 pass over group g (called by every lane of the
 //                                   warp, so ops may use warp collectives); returns bit q set
@@ -124,6 +142,13 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
     stage_image(t, smem, op.image_floats(t));   // ends with __syncthreads()
     const SmemView v = make_view(t, smem);
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // this lane's staging slot: vector k of the group at slot[k * blockDim] (conflict-free)
+    float4* const slot = reinterpret_cast<float4*>(reinterpret_cast<char*>(smem4) + image_bytes + kQueueBytes) + threadIdx.x;
+    if (Op::kStageVecs > 0) {
+        const int64_t gf = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+        if (gf < ngroups) op.stage(slot, gf);
+        cp_async_commit();
+    }
     // warp-uniform trip count: flush and some ops use warp-level synchronisation
     for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
         const int64_t g = g0 + lane;
@@ -131,7 +156,13 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
             const int64_t gp = g + stride * Op::kPrefetch;
             if (gp < ngroups) op.prefetch(gp);
         }
-        const unsigned m = op.hot(t, v, g, g < ngroups, lane);
+        unsigned m;
+        if (Op::kStageVecs > 0) {
+            cp_async_wait_all();
+            m = op.hot_staged(t, v, g, g < ngroups, slot, g + stride < ngroups ? g + stride : (int64_t)-1);
+        } else {
+            m = op.hot(t, v, g, g < ngroups, lane);
+        }
         if (m) {
 #pragma unroll
             for (int q = 0; q < Op::kVec; ++q)
@@ -181,8 +212,16 @@ struct QueryOp {
 #ifndef MERL_PF_QUERY
 #define MERL_PF_QUERY 1
 #endif
-    static constexpr int kPrefetch = MERL_PF_QUERY;
+#ifndef MERL_QUERY_STAGE
+#define MERL_QUERY_STAGE 1
+#endif
     static constexpr bool kEval = (MODE == MODE_EVAL || MODE == MODE_EVAL_PDF);
+    // Measured on B200 (profiles/r01_tuning.md section 8): the gather-free modes (pdf, bins) gain 8 %
+    // from staging their inputs through shared memory (199 / 206 Gquery/s = 85 / 88 % of HBM) and
+    // then want no L2 prefetch; the modes with a table gather lose 6-12 % with staging (the staged
+    // copies compete with the latency-critical gather for the load path) and keep the L2 prefetch.
+    static constexpr int kStageVecs = (MERL_QUERY_STAGE && VEC == 4 && !kEval) ? 6 : 0;
+    static constexpr int kPrefetch = kStageVecs ? 0 : MERL_PF_QUERY;
     static constexpr bool kPdf = (MODE == MODE_PDF || MODE == MODE_EVAL_PDF);
     QueryIn in;
     QueryOut out;
@@ -193,12 +232,34 @@ struct QueryOp {
         prefetch_stream<VEC>(in.wox, g); prefetch_stream<VEC>(in.woy, g); prefetch_stream<VEC>(in.woz, g);
     }
 
+    __device__ __forceinline__ void stage(float4* slot, const int64_t g) const {
+        cp_async16(slot + 0 * kThreadsPerCta, in.wix + 4 * g); cp_async16(slot + 1 * kThreadsPerCta, in.wiy + 4 * g);
+        cp_async16(slot + 2 * kThreadsPerCta, in.wiz + 4 * g); cp_async16(slot + 3 * kThreadsPerCta, in.wox + 4 * g);
+        cp_async16(slot + 4 * kThreadsPerCta, in.woy + 4 * g); cp_async16(slot + 5 * kThreadsPerCta, in.woz + 4 * g);
+    }
+    // inputs of group g come from the lane's slot; the slot is then re-armed with group g_next (< 0: none)
+    __device__ __forceinline__ unsigned hot_staged(const TableDev& t, const SmemView& v, const int64_t g,
+                                                   const bool in_range, float4* slot, const int64_t g_next) const {
+        if (!in_range) return 0u;
+        const Pack<4> ax = load_slot(slot, 0), ay = load_slot(slot, 1), az = load_slot(slot, 2),
+                      bx = load_slot(slot, 3), by = load_slot(slot, 4), bz = load_slot(slot, 5);
+        if (g_next >= 0) stage(slot, g_next);
+        cp_async_commit();
+        return body(t, v, g, reinterpret_cast<const Pack<VEC>&>(ax), reinterpret_cast<const Pack<VEC>&>(ay),
+                    reinterpret_cast<const Pack<VEC>&>(az), reinterpret_cast<const Pack<VEC>&>(bx),
+                    reinterpret_cast<const Pack<VEC>&>(by), reinterpret_cast<const Pack<VEC>&>(bz));
+    }
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int) const {
         if (!in_range) return 0u;
         const Pack<VEC> ax = load_stream<VEC>(in.wix, g), ay = load_stream<VEC>(in.wiy, g),
                         az = load_stream<VEC>(in.wiz, g), bx = load_stream<VEC>(in.wox, g),
                         by = load_stream<VEC>(in.woy, g), bz = load_stream<VEC>(in.woz, g);
+        return body(t, v, g, ax, ay, az, bx, by, bz);
+    }
+    __device__ __forceinline__ unsigned body(const TableDev& t, const SmemView& v, const int64_t g, const Pack<VEC>& ax,
+                                             const Pack<VEC>& ay, const Pack<VEC>& az, const Pack<VEC>& bx,
+                                             const Pack<VEC>& by, const Pack<VEC>& bz) const {
         const unsigned act = load_active<VEC>(in.active, g);
         int idx[VEC];
         Pack<VEC> pdf;
@@ -358,6 +419,9 @@ struct SampleOp {
 #define MERL_PF_SAMPLE 0
 #endif
     static constexpr int kPrefetch = MERL_PF_SAMPLE;
+    static constexpr int kStageVecs = 0;
+    __device__ __forceinline__ void stage(float4*, int64_t) const {}
+    __device__ __forceinline__ unsigned hot_staged(const TableDev&, const SmemView&, int64_t, bool, float4*, int64_t) const { return 0u; }
     SampleIn in;
     SampleOut out;
 
@@ -463,6 +527,11 @@ struct BackwardOp {
 #define MERL_PF_BACKWARD 0
 #endif
     static constexpr int kPrefetch = MERL_PF_BACKWARD;
+#ifndef MERL_BWD_STAGE
+#define MERL_BWD_STAGE 1
+#endif
+    // input staging (see cp_async16): only the big-batch path, which has no per-query gather
+    static constexpr int kStageVecs = (MERL_BWD_STAGE && VEC == 4 && !GATHER) ? 9 : 0;
     QueryIn q;
     const float *gr, *gg, *gb;
     float4* grad;
@@ -474,6 +543,29 @@ struct BackwardOp {
         prefetch_stream<VEC>(gr, g); prefetch_stream<VEC>(gg, g); prefetch_stream<VEC>(gb, g);
     }
 
+    __device__ __forceinline__ void stage(float4* slot, const int64_t g) const {
+        cp_async16(slot + 0 * kThreadsPerCta, q.wix + 4 * g); cp_async16(slot + 1 * kThreadsPerCta, q.wiy + 4 * g);
+        cp_async16(slot + 2 * kThreadsPerCta, q.wiz + 4 * g); cp_async16(slot + 3 * kThreadsPerCta, q.wox + 4 * g);
+        cp_async16(slot + 4 * kThreadsPerCta, q.woy + 4 * g); cp_async16(slot + 5 * kThreadsPerCta, q.woz + 4 * g);
+        cp_async16(slot + 6 * kThreadsPerCta, gr + 4 * g); cp_async16(slot + 7 * kThreadsPerCta, gg + 4 * g);
+        cp_async16(slot + 8 * kThreadsPerCta, gb + 4 * g);
+    }
+    // (an out-of-range lane still takes part, for the warp collectives of AGG; its slot holds stale
+    // data, which is harmless because its `act` is 0)
+    __device__ __forceinline__ unsigned hot_staged(const TableDev& t, const SmemView& v, const int64_t g,
+                                                   const bool in_range, float4* slot, const int64_t g_next) const {
+        if (!AGG && !in_range) return 0u;
+        const Pack<4> ax = load_slot(slot, 0), ay = load_slot(slot, 1), az = load_slot(slot, 2), bx = load_slot(slot, 3),
+                      by = load_slot(slot, 4), bz = load_slot(slot, 5), cr = load_slot(slot, 6), cg = load_slot(slot, 7),
+                      cb = load_slot(slot, 8);
+        if (g_next >= 0) stage(slot, g_next);
+        cp_async_commit();
+        const unsigned act = in_range ? load_active<VEC>(q.active, g) : 0u;
+        typedef const Pack<VEC>& R;
+        return body(t, v, g, in_range, threadIdx.x & 31, act, reinterpret_cast<R>(ax), reinterpret_cast<R>(ay),
+                    reinterpret_cast<R>(az), reinterpret_cast<R>(bx), reinterpret_cast<R>(by), reinterpret_cast<R>(bz),
+                    reinterpret_cast<R>(cr), reinterpret_cast<R>(cg), reinterpret_cast<R>(cb));
+    }
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
                                             const int lane) const {
         if (!AGG && !in_range) return 0u;
@@ -483,6 +575,13 @@ struct BackwardOp {
                         by = load_stream<VEC>(q.woy, gl), bz = load_stream<VEC>(q.woz, gl),
                         cr = load_stream<VEC>(gr, gl), cg = load_stream<VEC>(gg, gl), cb = load_stream<VEC>(gb, gl);
         const unsigned act = in_range ? load_active<VEC>(q.active, gl) : 0u;
+        return body(t, v, g, in_range, lane, act, ax, ay, az, bx, by, bz, cr, cg, cb);
+    }
+    __device__ __forceinline__ unsigned body(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                             const int lane, const unsigned act, const Pack<VEC>& ax, const Pack<VEC>& ay,
+                                             const Pack<VEC>& az, const Pack<VEC>& bx, const Pack<VEC>& by,
+                                             const Pack<VEC>& bz, const Pack<VEC>& cr, const Pack<VEC>& cg,
+                                             const Pack<VEC>& cb) const {
         int idx[VEC];
         bool emit[VEC];
         unsigned uncmask = 0;
@@ -568,6 +667,9 @@ __global__ void backward_mask_kernel(const float4* __restrict__ cells, float4* _
 struct EvalPdfAosOp {
     static constexpr int kVec = 1;
     static constexpr int kPrefetch = 0;
+    static constexpr int kStageVecs = 0;
+    __device__ __forceinline__ void stage(float4*, int64_t) const {}
+    __device__ __forceinline__ unsigned hot_staged(const TableDev&, const SmemView&, int64_t, bool, float4*, int64_t) const { return 0u; }
     const float4 *wi4, *wo4;
     float4* out4;
 
@@ -603,6 +705,9 @@ struct EvalPdfAosOp {
 struct SampleAosOp {
     static constexpr int kVec = 1;
     static constexpr int kPrefetch = 0;
+    static constexpr int kStageVecs = 0;
+    __device__ __forceinline__ void stage(float4*, int64_t) const {}
+    __device__ __forceinline__ unsigned hot_staged(const TableDev&, const SmemView&, int64_t, bool, float4*, int64_t) const { return 0u; }
     const float4 *wi4, *u4;
     float4 *wo4, *w4;
 
