@@ -1165,7 +1165,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     const size_t nf = 19, ni = 4;
     size_t bytes = cap * (nf * 4 + ni * 4) + cap * 16 * 9 + 256;
     bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(4 * ntables + 4) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
-    bytes += (size_t)cap * 4 * 2 + 512 + 256 + (size_t)kMaxClusters * 16 + 256 + 256;   // live lists, their counters, clusters, pass info
+    bytes += (size_t)cap * 4 * 2 + 512 + 256 + (size_t)kMaxClusters * 32 + 256 + 256;   // live lists, their counters, clusters, pass info
     char* ws = nullptr;
     if (cudaMemPool_t pool = render_pool(t0->device)) CUDA_TRY(cudaMallocFromPoolAsync((void**)&ws, bytes, pool, s));
     else CUDA_TRY(cudaMallocAsync(&ws, bytes, s));
@@ -1187,12 +1187,13 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     unsigned long long* d_nq = reinterpret_cast<unsigned long long*>(take(8));
     int* d_live[2] = {reinterpret_cast<int*>(take((size_t)cap * 4)), reinterpret_cast<int*>(take((size_t)cap * 4))};
     int* d_nlive = reinterpret_cast<int*>(take(2 * 4));
-    float4* d_clus = reinterpret_cast<float4*>(take((size_t)kMaxClusters * 16));
+    ClusterBox* d_clus = reinterpret_cast<ClusterBox*>(take((size_t)kMaxClusters * sizeof(ClusterBox)));
     PassInfo* d_pass = reinterpret_cast<PassInfo*>(take(sizeof(PassInfo)));
 
     // Spheres along a Morton curve, kClusterSize consecutive ones under one bounding sphere
     // (merl_render.cuh: intersect_spheres).  The device only ever uses the sorted order.
-    std::vector<float4> hs(nspheres), hc((nspheres + kClusterSize - 1) / kClusterSize);
+    std::vector<float4> hs(nspheres);
+    std::vector<ClusterBox> hc((nspheres + kClusterSize - 1) / kClusterSize);
     std::vector<int> hm(nspheres);
     {
         float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
@@ -1224,15 +1225,14 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         }
         for (size_t g = 0; g < hc.size(); ++g) {
             const int s0 = (int)g * kClusterSize, s1 = std::min(s0 + kClusterSize, nspheres);
-            double c[3] = {0, 0, 0};
-            for (int k = s0; k < s1; ++k) { c[0] += hs[k].x; c[1] += hs[k].y; c[2] += hs[k].z; }
-            for (int a = 0; a < 3; ++a) c[a] /= (s1 - s0);
-            double r = 0;
+            float lo3[3] = {3e38f, 3e38f, 3e38f}, hi3[3] = {-3e38f, -3e38f, -3e38f};
             for (int k = s0; k < s1; ++k) {
-                const double dx = hs[k].x - c[0], dy = hs[k].y - c[1], dz = hs[k].z - c[2];
-                r = std::max(r, std::sqrt(dx * dx + dy * dy + dz * dz) + (double)hs[k].w);
+                const float c[3] = {hs[k].x, hs[k].y, hs[k].z};
+                const float pad = hs[k].w * (1.f + 1e-4f) + 1e-5f;   // conservative
+                for (int a = 0; a < 3; ++a) { lo3[a] = std::min(lo3[a], c[a] - pad); hi3[a] = std::max(hi3[a], c[a] + pad); }
             }
-            hc[g] = make_float4((float)c[0], (float)c[1], (float)c[2], (float)(r * (1.0 + 1e-4) + 1e-5));   // conservative
+            hc[g].lo = make_float4(lo3[0], lo3[1], lo3[2], 0.f);
+            hc[g].hi = make_float4(hi3[0], hi3[1], hi3[2], 0.f);
         }
     }
     std::vector<TableDev> ht(ntables);
@@ -1259,7 +1259,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     {
     RT_TRY(cudaMemcpyAsync(d_sph, hs.data(), sizeof(float4) * nspheres, cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemcpyAsync(d_smat, hm.data(), sizeof(int) * nspheres, cudaMemcpyHostToDevice, s));
-    RT_TRY(cudaMemcpyAsync(d_clus, hc.data(), sizeof(float4) * hc.size(), cudaMemcpyHostToDevice, s));
+    RT_TRY(cudaMemcpyAsync(d_clus, hc.data(), sizeof(ClusterBox) * hc.size(), cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemcpyAsync(d_tabs, ht.data(), sizeof(TableDev) * ntables, cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int) * ntables, s));
     RT_TRY(cudaMemsetAsync(d_nq, 0, 8, s));

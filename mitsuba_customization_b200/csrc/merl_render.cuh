@@ -69,32 +69,35 @@ __device__ __forceinline__ void film_add(float4* film, int pixel, float r, float
 }
 
 // Two-level intersection.  The host sorts the spheres along a Morton curve and groups kClusterSize
-// consecutive ones under a bounding sphere (merl_render); a ray tests the bound first and skips the
-// group when it misses it, when the bound lies behind the origin, or when it starts beyond the best
+// consecutive ones under an axis-aligned bounding box (merl_render); a ray tests the box first and skips the
+// group when it misses it, when the box lies behind the origin, or when it starts beyond the best
 // hit so far.  The per-sphere arithmetic is the brute-force loop's (and the oracle's), so the nearest
 // hit is the same one; only exact ties in t could resolve to another sphere.
 constexpr int kClusterSize = 8;
 constexpr int kMaxClusters = kMaxSpheres / kClusterSize;
 
-// ray vs bounding sphere: false = no sphere inside can be hit in (kRayEps, t_max)
-__device__ __forceinline__ bool cluster_may_hit(const float4 c, float ox, float oy, float oz, float dx, float dy,
-                                                float dz, float t_max) {
-    const float lx = ox - c.x, ly = oy - c.y, lz = oz - c.z;
-    const float b = lx * dx + ly * dy + lz * dz;
-    const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
-    const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
-    if (disc < 0.f) return false;
-    const float sq = sqrtf(disc);
-    return (-b + sq >= kRayEps) && (-b - sq <= t_max);
+// ray vs the group's axis-aligned bounding box (slab test): false = no sphere inside can be hit in
+// (kRayEps, t_max).  The box is padded on the host, so a ray lying exactly in one of its faces cannot
+// touch a sphere and the NaN that 0 * inf produces there (fminf / fmaxf drop it) is harmless.
+struct ClusterBox { float4 lo, hi; };
+__device__ __forceinline__ bool cluster_may_hit(const ClusterBox c, float ox, float oy, float oz, float idx, float idy,
+                                                float idz, float t_max) {
+    const float x0 = (c.lo.x - ox) * idx, x1 = (c.hi.x - ox) * idx;
+    const float y0 = (c.lo.y - oy) * idy, y1 = (c.hi.y - oy) * idy;
+    const float z0 = (c.lo.z - oz) * idz, z1 = (c.hi.z - oz) * idz;
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), kRayEps));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+    return !(tn > tf);
 }
 
 // nearest hit of (o, d) with the spheres in shared memory; returns sphere index or -1
-__device__ __forceinline__ int intersect_spheres(const float4* sph, const float4* clus, int n, float ox, float oy,
+__device__ __forceinline__ int intersect_spheres(const float4* sph, const ClusterBox* clus, int n, float ox, float oy,
                                                  float oz, float dx, float dy, float dz, float& t_hit) {
     int best = -1;
     float tb = 3.0e38f;
+    const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
     for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize) {
-        if (!cluster_may_hit(clus[k], ox, oy, oz, dx, dy, dz, tb)) continue;
+        if (!cluster_may_hit(clus[k], ox, oy, oz, idx, idy, idz, tb)) continue;
         const int s1 = min(s0 + kClusterSize, n);
         for (int s = s0; s < s1; ++s) {
             const float4 c = sph[s];
@@ -114,10 +117,11 @@ __device__ __forceinline__ int intersect_spheres(const float4* sph, const float4
     t_hit = tb;
     return best;
 }
-__device__ __forceinline__ bool occluded(const float4* sph, const float4* clus, int n, float ox, float oy, float oz,
+__device__ __forceinline__ bool occluded(const float4* sph, const ClusterBox* clus, int n, float ox, float oy, float oz,
                                          float dx, float dy, float dz) {
+    const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
     for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize) {
-        if (!cluster_may_hit(clus[k], ox, oy, oz, dx, dy, dz, 3.0e38f)) continue;
+        if (!cluster_may_hit(clus[k], ox, oy, oz, idx, idy, idz, 3.0e38f)) continue;
         const int s1 = min(s0 + kClusterSize, n);
         for (int s = s0; s < s1; ++s) {
             const float4 c = sph[s];
@@ -203,7 +207,7 @@ struct LiveList {
 };
 
 __device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
-                                          const float4* clus, const int* smat, const int i, const int depth,
+                                          const ClusterBox* clus, const int* smat, const int i, const int depth,
                                           float4* __restrict__ film, unsigned long long* __restrict__ nquery) {
     const int pixel = P.pixel[i];
     const float4 dead = make_float4(0.f, 0.f, -1.f, 0.f);
@@ -269,13 +273,13 @@ __device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P
 
 __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const PathState P, const StageBuf S,
                                                        const float4* __restrict__ spheres,
-                                                       const float4* __restrict__ clusters,
+                                                       const ClusterBox* __restrict__ clusters,
                                                        const int* __restrict__ sphere_mat,
                                                        const PassInfo* __restrict__ pass, const int depth,
                                                        float4* __restrict__ film,
                                                        unsigned long long* __restrict__ nquery, const LiveList L) {
     __shared__ float4 sph[kMaxSpheres];
-    __shared__ float4 clus[kMaxClusters];
+    __shared__ ClusterBox clus[kMaxClusters];
     __shared__ int smat[kMaxSpheres];
     const int count = L.in ? *L.count_in : pass->np;
     if (blockIdx.x * blockDim.x >= count) return;          // whole CTA beyond the live range
