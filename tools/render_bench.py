@@ -67,19 +67,9 @@ def main():
            "mean_radiance": [float(x) for x in film[..., :3].mean(dim=(0, 1))],
            "sample_share_min_max": [float(film[..., 3].min()), float(film[..., 3].max())]}
     if "--cpu" in sys.argv and rank == 0:
-        from oracle import merl_oracle as O, render_oracle as RO
-        orcs = [O.OracleTable(synth.synthetic_table(k), cdf=b.cdf().cpu().numpy()) for k, b in enumerate(sc.bsdfs)]
-        cs = max(1, spp // 16)
-        t0 = time.time()
-        ref = RO.render(orcs, sc.spheres, width=w, height=h, spp=spp, max_depth=depth, seed=1, cam_pos=sc.cam_pos,
-                        cam_target=sc.cam_target, cam_up=sc.cam_up, fov_x_deg=sc.fov_x_deg, env=sc.env, spp_begin=0, spp_end=cs)
-        dt = time.time() - t0
-        out["cpu_oracle_spp_mpix_per_s"] = cs * w * h / 1e6 / dt
-        out["cpu_oracle_threads"] = O.max_threads()
-        out["cpu_oracle_sample"] = f"{cs} of {spp} spp, {dt:.1f} s"
-        if world == 1:   # same seed, same samples: the first cs spp must agree as an image
-            part = RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=(0, cs)).cpu().numpy()
-            out["relmse_vs_oracle_first_spp"] = float(((part[..., :3] - ref[..., :3]) ** 2).mean() / (ref[..., :3] ** 2).mean())
+        from tests.render_cpu_baseline import cpu_render_baseline   # the oracle is test infrastructure
+        gpu = (lambda r: RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=r).cpu().numpy()) if world == 1 else None
+        out.update(cpu_render_baseline(sc, w, h, spp, depth, 1, gpu))
     if rank == 0:
         print(json.dumps(out), flush=True)
     if comm is not None:
