@@ -1162,8 +1162,8 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     cap = (cap + 255) & ~(int64_t)255;
 
     // one stream-ordered workspace: path state, stage buffers, sort scratch, scene
-    const size_t nf = 19, ni = 4;
-    size_t bytes = cap * (nf * 4 + ni * 4) + cap * 16 * 9 + 256;
+    const size_t nf4 = 6, ni = 4;   // path state: six float4 and four int arrays
+    size_t bytes = cap * (nf4 * 16 + ni * 4) + cap * 16 * 9 + 512;
     bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(4 * ntables + 4) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
     bytes += (size_t)cap * 4 * 2 + 512 + 256 + (size_t)kMaxClusters * 32 + 256 + 256;   // live lists, their counters, clusters, pass info
     char* ws = nullptr;
@@ -1174,11 +1174,9 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     float4* f4 = reinterpret_cast<float4*>(take(cap * 16 * 9));
     StageBuf A{f4, f4 + cap, f4 + 2 * cap, f4 + 3 * cap, f4 + 4 * cap, f4 + 5 * cap};
     StageBuf B{f4 + 6 * cap, f4 + 7 * cap, f4 + 8 * cap, A.fe4, A.wos4, A.w4};
-    float* fl = reinterpret_cast<float*>(take(cap * nf * 4));
+    float4* ps = reinterpret_cast<float4*>(take(cap * nf4 * 16));
     int* in = reinterpret_cast<int*>(take(cap * ni * 4));
-    PathState P{fl, fl + cap, fl + 2 * cap, fl + 3 * cap, fl + 4 * cap, fl + 5 * cap, fl + 6 * cap, fl + 7 * cap,
-                fl + 8 * cap, fl + 9 * cap, fl + 10 * cap, fl + 11 * cap, fl + 12 * cap, fl + 13 * cap, fl + 14 * cap,
-                fl + 15 * cap, fl + 16 * cap, fl + 17 * cap, fl + 18 * cap, in, in + cap, in + 2 * cap, in + 3 * cap};
+    PathState P{ps, ps + cap, ps + 2 * cap, ps + 3 * cap, ps + 4 * cap, ps + 5 * cap, in, in + cap, in + 2 * cap, in + 3 * cap};
     float4* d_sph = reinterpret_cast<float4*>(take((size_t)nspheres * 16));
     int* d_smat = reinterpret_cast<int*>(take((size_t)nspheres * 4));
     int* d_counts = reinterpret_cast<int*>(take((size_t)(4 * ntables + 4) * 4));

@@ -47,18 +47,20 @@ struct RenderDev {
     Camera cam;
 };
 
-// Path state of one wavefront pass, SoA over `cap` paths (device workspace).
+// Path state of one wavefront pass over `cap` paths (device workspace).  From the second bounce on
+// the kernels reach it through the live list / the stage slots, i.e. in scattered order, so related
+// scalars share a float4 (one 16-byte access, half a sector) instead of one array each.
 struct PathState {
-    float *ox, *oy, *oz, *dx, *dy, *dz;       // current ray
-    float *tr, *tg, *tb;                      // throughput
-    float *lr, *lg, *lb;                      // accumulated radiance
-    float* prev_pdf;                          // solid-angle pdf of the direction that produced the ray (0 = camera)
-    float *nx, *ny, *nz;                      // shading normal at the current hit
-    float *hx, *hy, *hz;                      // hit point
-    int* pixel;                               // -1 = dead
+    float4* org;      // ray origin, .w = solid-angle pdf of the direction that produced the ray (0 = camera)
+    float4* dir;      // ray direction
+    float4* thr;      // throughput
+    float4* rad;      // accumulated radiance
+    float4* nrm;      // shading normal at the current hit
+    float4* hit;      // hit point
+    int* pixel;       // -1 = dead
     int* sample;
-    int* slot;                                // indexed by stage slot: the path whose query sits in that slot
-    int* mat;                                 // material at the current hit, -1 when the path has no query this bounce
+    int* slot;        // indexed by stage slot: the path whose query sits in that slot
+    int* mat;         // material at the current hit, -1 when the path has no query this bounce
 };
 
 constexpr int kMaxSpheres = 256;
@@ -180,11 +182,10 @@ __global__ void rt_raygen_kernel(const RenderDev R, const PathState P, const Pas
     const Camera& c = R.cam;
     float dx = c.fx + sx * c.rx + sy * c.ux, dy = c.fy + sx * c.ry + sy * c.uy, dz = c.fz + sx * c.rz + sy * c.uz;
     const float inv = rsqrtf(dx * dx + dy * dy + dz * dz);
-    P.ox[i] = c.px; P.oy[i] = c.py; P.oz[i] = c.pz;
-    P.dx[i] = dx * inv; P.dy[i] = dy * inv; P.dz[i] = dz * inv;
-    P.tr[i] = 1.f; P.tg[i] = 1.f; P.tb[i] = 1.f;
-    P.lr[i] = 0.f; P.lg[i] = 0.f; P.lb[i] = 0.f;
-    P.prev_pdf[i] = 0.f;
+    P.org[i] = make_float4(c.px, c.py, c.pz, 0.f);
+    P.dir[i] = make_float4(dx * inv, dy * inv, dz * inv, 0.f);
+    P.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+    P.rad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     P.pixel[i] = pixel; P.sample[i] = s;
     P.mat[i] = -1;
 }
@@ -212,15 +213,18 @@ __device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P
     const int pixel = P.pixel[i];
     const float4 dead = make_float4(0.f, 0.f, -1.f, 0.f);
     if (pixel < 0) { P.mat[i] = -1; S.wi4[i] = dead; S.woe4[i] = dead; return; }
-    const float ox = P.ox[i], oy = P.oy[i], oz = P.oz[i], dx = P.dx[i], dy = P.dy[i], dz = P.dz[i];
+    const float4 o4 = P.org[i], d4 = P.dir[i];
+    const float ox = o4.x, oy = o4.y, oz = o4.z, dx = d4.x, dy = d4.y, dz = d4.z;
     float t;
     const int hit = intersect_spheres(sph, clus, R.nspheres, ox, oy, oz, dx, dy, dz, t);
     bool finish = false;
-    float lr = P.lr[i], lg = P.lg[i], lb = P.lb[i];
+    const float4 l4 = P.rad[i];
+    float lr = l4.x, lg = l4.y, lb = l4.z;
     if (hit < 0) {
         // escaped: environment radiance, MIS against the emitter sample of the previous bounce
-        const float w = depth == 0 ? 1.f : power_heuristic(P.prev_pdf[i], 0.0795774715f);
-        lr = fmaf(P.tr[i] * R.env[0], w, lr); lg = fmaf(P.tg[i] * R.env[1], w, lg); lb = fmaf(P.tb[i] * R.env[2], w, lb);
+        const float w = depth == 0 ? 1.f : power_heuristic(o4.w, 0.0795774715f);
+        const float4 t4 = P.thr[i];
+        lr = fmaf(t4.x * R.env[0], w, lr); lg = fmaf(t4.y * R.env[1], w, lg); lb = fmaf(t4.z * R.env[2], w, lb);
         finish = true;
     } else if (depth >= R.max_depth) {
         finish = true;   // interaction budget used up
@@ -263,8 +267,8 @@ __device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P
         const unsigned live = __activemask();
         if ((threadIdx.x & 31) == __ffs(live) - 1) atomicAdd(nquery, (unsigned long long)__popc(live));
     }
-    P.lr[i] = lr; P.lg[i] = lg; P.lb[i] = lb;
-    P.nx[i] = nx; P.ny[i] = ny; P.nz[i] = nz; P.hx[i] = hx; P.hy[i] = hy; P.hz[i] = hz;
+    P.nrm[i] = make_float4(nx, ny, nz, 0.f);
+    P.hit[i] = make_float4(hx, hy, hz, 0.f);
     P.mat[i] = m;
     S.wi4[i] = make_float4(wix, wiy, wiz, (float)m);
     S.woe4[i] = woe;
@@ -409,26 +413,26 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
 __device__ __forceinline__ bool shade_one(const RenderDev& R, const PathState& P, const StageBuf& S, const int slot,
                                           const int i, float4* __restrict__ film) {
     const float4 fe = S.fe4[slot], ws = S.wos4[slot], w = S.w4[slot];
-    float tr = P.tr[i], tg = P.tg[i], tb = P.tb[i];
+    const float4 t4 = P.thr[i], l4 = P.rad[i];
+    float tr = t4.x, tg = t4.y, tb = t4.z;
     const float mis = power_heuristic(0.0795774715f, fe.w) * 12.5663706f;   // weight / pdf_e
-    const float lr = fmaf(tr * fe.x * R.env[0], mis, P.lr[i]), lg = fmaf(tg * fe.y * R.env[1], mis, P.lg[i]),
-                lb = fmaf(tb * fe.z * R.env[2], mis, P.lb[i]);
+    const float lr = fmaf(tr * fe.x * R.env[0], mis, l4.x), lg = fmaf(tg * fe.y * R.env[1], mis, l4.y),
+                lb = fmaf(tb * fe.z * R.env[2], mis, l4.z);
     tr *= w.x; tg *= w.y; tb *= w.z;
     if (!(ws.w > 0.f) || !(tr + tg + tb > 0.f)) {
         film_add(film, P.pixel[i], lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
         P.pixel[i] = -1; P.mat[i] = -1;
         return false;
     }
-    const float nx = P.nx[i], ny = P.ny[i], nz = P.nz[i];
+    const float4 n4 = P.nrm[i], h4 = P.hit[i];
+    const float nx = n4.x, ny = n4.y, nz = n4.z;
     float s[3], tt[3];
     frame_from_normal(nx, ny, nz, s, tt);
-    P.dx[i] = ws.x * s[0] + ws.y * tt[0] + ws.z * nx;
-    P.dy[i] = ws.x * s[1] + ws.y * tt[1] + ws.z * ny;
-    P.dz[i] = ws.x * s[2] + ws.y * tt[2] + ws.z * nz;
-    P.ox[i] = fmaf(kRayEps, nx, P.hx[i]); P.oy[i] = fmaf(kRayEps, ny, P.hy[i]); P.oz[i] = fmaf(kRayEps, nz, P.hz[i]);
-    P.tr[i] = tr; P.tg[i] = tg; P.tb[i] = tb;
-    P.lr[i] = lr; P.lg[i] = lg; P.lb[i] = lb;
-    P.prev_pdf[i] = ws.w;
+    P.dir[i] = make_float4(ws.x * s[0] + ws.y * tt[0] + ws.z * nx, ws.x * s[1] + ws.y * tt[1] + ws.z * ny,
+                           ws.x * s[2] + ws.y * tt[2] + ws.z * nz, 0.f);
+    P.org[i] = make_float4(fmaf(kRayEps, nx, h4.x), fmaf(kRayEps, ny, h4.y), fmaf(kRayEps, nz, h4.z), ws.w);
+    P.thr[i] = make_float4(tr, tg, tb, 0.f);
+    P.rad[i] = make_float4(lr, lg, lb, 0.f);
     return true;
 }
 
