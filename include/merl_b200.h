@@ -89,6 +89,10 @@ int merl_table_destroy(merl_table_t* t);
 int merl_table_info(const merl_table_t* t, merl_table_info_t* out);
 /* Replace the sampler CDF (host float[ni][nh+1]); the density table is re-derived. */
 int merl_table_set_cdf(merl_table_t* t, const float* cdf_host);
+/* After the caller has modified the float4 table in place on the device (d_cells is the
+ * differentiable parameter): rebuild the sampler CDF rows and densities from it, asynchronously
+ * on `stream`.  Mitsuba 3: parameters_changed({"data"}). */
+int merl_table_refresh_sampler(merl_table_t* t, merl_stream_t stream);
 /* Copy tables back to the host; any pointer may be NULL.  Synchronous. */
 int merl_table_download(const merl_table_t* t, float* cells4_host, float* cdf_host, float* dens_host);
 

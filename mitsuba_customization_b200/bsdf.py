@@ -179,6 +179,11 @@ class MERL:
         """Differentiable parameters, as `traverse(TraversalCallback*)` would expose them."""
         return {"data": self.cells()}
 
+    def parameters_changed(self, keys=()):
+        """After `data` (cells()) was updated in place, e.g. by an optimiser step: rebuild the sampler."""
+        if not keys or "data" in keys:
+            check(_cabi.lib().merl_table_refresh_sampler(self._h, _stream(self.device)))
+
     def cells(self) -> torch.Tensor:
         """The prescaled float4 table on the device, (ncell, 4), zero-copy."""
         return torch.as_tensor(_DevArray(self.info.d_cells, (self.info.ncell, 4)), device=self.device)

@@ -539,6 +539,15 @@ extern "C" int merl_table_set_cdf(merl_table_t* t, const float* cdf_host) {
     return MERL_OK;
 }
 
+// The float4 table is the differentiable parameter (merl_table_info_t.d_cells); an optimiser updates
+// it in place on the device.  This re-derives what depends on it -- the sampler's CDF rows and the
+// density table -- asynchronously on `stream` (Mitsuba 3: parameters_changed({"data"})).
+extern "C" int merl_table_refresh_sampler(merl_table_t* t, merl_stream_t stream) {
+    if (!t) return fail(MERL_ERR_ARG, "NULL argument");
+    DeviceGuard g(t->device);
+    return upload_sampler(t, nullptr, (cudaStream_t)stream);
+}
+
 extern "C" int merl_table_download(const merl_table_t* t, float* cells4, float* cdf, float* dens) {
     if (!t) return fail(MERL_ERR_ARG, "NULL argument");
     DeviceGuard g(t->device);
@@ -1298,7 +1307,10 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         rt_advance_kernel<<<1, 1, 0, q>>>(d_pass, (long long)total, (int)cap);
     };
     const int64_t per_pass = 3 + 7 * (int64_t)p->max_depth;
-    if (npasses >= 2 && g_render_graphs.load()) {
+    // (a caller that is itself capturing `stream` gets the plain launches: they become part of its graph)
+    cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) { cudaGetLastError(); cap_status = cudaStreamCaptureStatusNone; }
+    if (npasses >= 2 && g_render_graphs.load() && cap_status == cudaStreamCaptureStatusNone) {
         RenderSide* side = render_side(t0->device);
         if (!side) { rc = MERL_ERR_CUDA; goto done; }
         std::lock_guard<std::mutex> lk(side->mu);

@@ -17,6 +17,8 @@
 #include <mitsuba/core/properties.h>
 #include <mitsuba/render/bsdf.h>
 
+#include <algorithm>
+
 #include "../common/merl_host.h"
 
 NAMESPACE_BEGIN(mitsuba)
@@ -161,6 +163,11 @@ public:
     // dr::CustomOp in INTEGRATION.md §2 calls backward_table() from its backward().
     void traverse(TraversalCallback* cb) override {
         cb->put_parameter("data", m_info.d_cells, +ParamFlags::Differentiable);
+    }
+
+    void parameters_changed(const std::vector<std::string>& keys = {}) override {
+        if (keys.empty() || std::find(keys.begin(), keys.end(), "data") != keys.end())
+            check(merl_table_refresh_sampler(m_table.get(), jit_cuda_stream()), "rebuilding the sampler");
     }
 
     // grad_cells4: device float4[ncell] (zeroed by the caller) += d eval / d data . grad_out.

@@ -439,3 +439,26 @@ def test_non_finite_and_unnormalised_inputs_are_safe(plug, orc):
     ref = orc.bins(wi2, wo2)
     got = plug.bins(_si(wi2), torch.from_numpy(np.ascontiguousarray(wo2)).cuda()).cpu().numpy()
     assert np.array_equal(got[ref["stable"]], ref["idx"][ref["stable"]])
+
+
+def test_parameters_changed_rebuilds_the_sampler(raw_table):
+    """The float4 table is the differentiable parameter: after an in-place update on the device,
+    parameters_changed() must leave the plugin identical to one built from the updated table."""
+    from mitsuba_customization_b200 import bsdf, synth
+    plug = bsdf.MERL(data=raw_table, device="cuda:0")
+    before = plug.cdf().clone()
+    plug.cells()[:, 0] *= 4.0          # an exact fp32 update, so the comparison below can be bitwise
+    plug.cells()[: plug.info.ncell // 3, 1] *= 0.25
+    plug.parameters_changed(["data"])
+    raw2 = raw_table.copy()
+    raw2[0] *= 4.0
+    raw2[1, : plug.info.ncell // 3] *= 0.25
+    fresh = bsdf.MERL(data=raw2, device="cuda:0")
+    assert torch.equal(plug.cells(), fresh.cells())
+    assert torch.equal(plug.cdf(), fresh.cdf()) and torch.equal(plug.dens(), fresh.dens())
+    assert not torch.equal(plug.cdf(), before)
+    wi, _ = synth.random_queries(1 << 14, seed=4)
+    u1, u2 = torch.rand(1 << 14, device="cuda"), torch.rand(2, 1 << 14, device="cuda")
+    a, wa = plug.sample(_ctx(), _si(wi), u1, u2)
+    b, wb = fresh.sample(_ctx(), _si(wi), u1, u2)
+    assert torch.equal(a.wo, b.wo) and torch.equal(a.pdf, b.pdf) and torch.equal(wa, wb)
