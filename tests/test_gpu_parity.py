@@ -462,3 +462,31 @@ def test_parameters_changed_rebuilds_the_sampler(raw_table):
     a, wa = plug.sample(_ctx(), _si(wi), u1, u2)
     b, wb = fresh.sample(_ctx(), _si(wi), u1, u2)
     assert torch.equal(a.wo, b.wo) and torch.equal(a.pdf, b.pdf) and torch.equal(wa, wb)
+
+
+def test_one_newton_step_recovers_the_table(raw_table):
+    """Forward + backward as an optimiser uses them.  eval is linear in the table with a diagonal
+    Gauss-Newton matrix (each query touches one cell), so from a wrong table one Newton step
+    cell -= (sum_q r_q cos_q) / (sum_q cos_q^2), both sums formed by merl_backward, must reproduce
+    the target's radiance on every query."""
+    from mitsuba_customization_b200 import bsdf, synth
+    target = bsdf.MERL(data=raw_table, device="cuda:0")
+    wrong = raw_table.copy()
+    wrong[wrong > 0] *= 0.5
+    plug = bsdf.MERL(data=wrong, device="cuda:0")
+    n = 1 << 21
+    wi, wo = synth.random_queries(n, seed=91)
+    si, two = _si(wi), torch.from_numpy(wo).cuda()
+    want = target.eval(_ctx(), si, two)
+    resid = plug.eval(_ctx(), si, two) - want
+    loss0 = float((resid.double() ** 2).sum())
+    grad = plug.backward(si, two, resid.contiguous(), warp_aggregate=False)               # J^T r
+    hess = plug.backward(si, two, two[2].expand(3, n).contiguous(), warp_aggregate=False)  # J^T J (diagonal)
+    cells = plug.cells()
+    hit = hess[:, :3] > 0
+    cells[:, :3][hit] -= (grad[:, :3][hit] / hess[:, :3][hit])
+    plug.parameters_changed(["data"])
+    got = plug.eval(_ctx(), si, two)
+    loss1 = float(((got - want).double() ** 2).sum())
+    assert loss1 < 1e-8 * loss0
+    _close(got.cpu().numpy(), want.cpu().numpy(), "radiance after one Newton step")
