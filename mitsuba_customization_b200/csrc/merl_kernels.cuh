@@ -50,8 +50,8 @@ template <> __device__ __forceinline__ void store_stream<4>(float* p, int64_t g,
 // L2 prefetch of what a lane will stream Op::kPrefetch iterations from now: moves the HBM latency off
 // the load's critical path at no register cost.  Measured on B200 (2^26 queries, profiles/
 // r01_tuning.md): eval+pdf 109 -> 117 Gquery/s, eval 125 -> 131 at distance 1; distance 2 is no better;
-// the sample and backward kernels (more streams per query, so more L2 pressure per iteration) lose
-// 1-5 %, so only the query kernels use it.
+// the backward kernels lose 5 %.  The sample kernel lost 1 % while it was instruction-bound and gains
+// 3 % (64.5 -> 66.7) since the sampler work that cut its instruction count by 15 %.
 template <int VEC> __device__ __forceinline__ void prefetch_stream(const float* p, int64_t g) {
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p + g * VEC));
 }
@@ -416,7 +416,7 @@ template <int VEC, int SEARCH>
 struct SampleOp {
     static constexpr int kVec = VEC;
 #ifndef MERL_PF_SAMPLE
-#define MERL_PF_SAMPLE 0
+#define MERL_PF_SAMPLE 1
 #endif
     static constexpr int kPrefetch = MERL_PF_SAMPLE;
     static constexpr int kStageVecs = 0;
