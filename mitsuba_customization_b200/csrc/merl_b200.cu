@@ -1270,6 +1270,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     RT_TRY(cudaMemcpyAsync(d_tabs, ht.data(), sizeof(TableDev) * ntables, cudaMemcpyHostToDevice, s));
     RT_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int) * ntables, s));
     RT_TRY(cudaMemsetAsync(d_nq, 0, 8, s));
+    RT_TRY(cudaMemsetAsync(d_nlive, 0, 8, s));
     float4* film = reinterpret_cast<float4*>(film4);
     const PassInfo pass0{0, (int)std::min<int64_t>(cap, total), 0};
     RT_TRY(cudaMemcpyAsync(d_pass, &pass0, sizeof pass0, cudaMemcpyHostToDevice, s));
@@ -1282,15 +1283,15 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     // stream that is forked from and joined back into the caller's stream with events: the call
     // stays asynchronous and ordered on `stream`.
     auto enqueue_pass = [&](cudaStream_t q) {
-        rt_raygen_kernel<<<nb, 256, 0, q>>>(R, P, d_pass);
-        // from depth 1 on the kernels walk the live list (grid-stride over a grid that covers a few
-        // waves; CTAs beyond the live count exit at once)
-        const int nbl = std::min(nb, t0->num_sms * 16);
+        // depth 0: camera rays and their first intersection in one kernel over the whole pass; its
+        // hits form the depth-0 live list.  Every other kernel walks a live list (grid-stride over
+        // a grid that covers a few waves; CTAs beyond the live count exit at once).
+        rt_primary_kernel<<<nb, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_nq, d_live[0], d_nlive);
+        const int g = std::min(nb, t0->num_sms * 16);
         for (int depth = 0; depth <= p->max_depth; ++depth) {
             const int cur = depth & 1, nxt = cur ^ 1;
-            const LiveList L{depth ? d_live[cur] : nullptr, d_nlive + cur, d_live[nxt], d_nlive + nxt};
-            const int g = depth ? nbl : nb;
-            rt_trace_kernel<<<g, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, d_nq, L);
+            const LiveList L{d_live[cur], d_nlive + cur, d_live[nxt], d_nlive + nxt};
+            if (depth) rt_trace_kernel<<<g, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, d_nq, L);
             if (depth == p->max_depth) break;   // the last trace only collects escaped paths
             // live queries -> contiguous, material-sorted segments (with one table this is plain
             // stream compaction: the BSDF stage then touches live queries only)
@@ -1304,9 +1305,9 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
                 d_tabs, ntables, d_seg, d_items, SampleAosOp{B.wi4, B.u4, B.wos4, B.w4}, img_f);
             rt_shade_kernel<<<g, 256, 0, q>>>(R, P, B, d_seg + ntables, film, L);
         }
-        rt_advance_kernel<<<1, 1, 0, q>>>(d_pass, (long long)total, (int)cap);
+        rt_advance_kernel<<<1, 1, 0, q>>>(d_pass, (long long)total, (int)cap, d_nlive);
     };
-    const int64_t per_pass = 3 + 7 * (int64_t)p->max_depth;
+    const int64_t per_pass = 2 + 7 * (int64_t)p->max_depth;
     // (a caller that is itself capturing `stream` gets the plain launches: they become part of its graph)
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) { cudaGetLastError(); cap_status = cudaStreamCaptureStatusNone; }

@@ -161,33 +161,30 @@ struct PassInfo {
     int np;            // paths in this pass (<= cap)
     int pad;
 };
-__global__ void rt_advance_kernel(PassInfo* pass, const long long total, const int cap) {
+__global__ void rt_advance_kernel(PassInfo* pass, const long long total, const int cap, int* primary_live_count) {
     const long long first = pass->first + cap;
     const long long left = total - first;
     pass->first = first;
     pass->np = left >= cap ? cap : (left > 0 ? (int)left : 0);
+    *primary_live_count = 0;   // the next pass's primary kernel appends its hits from zero
 }
 
-__global__ void rt_raygen_kernel(const RenderDev R, const PathState P, const PassInfo* __restrict__ pass) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= pass->np) return;
-    const int64_t gid = pass->first + i;
+// camera ray of path i of the pass <-> global sample (first + i); Philox stream (pixel, sample, 0)
+__device__ __forceinline__ void camera_ray(const RenderDev& R, const int64_t gid, int& pixel, int& s, float4& o4,
+                                           float4& d4) {
     const int npix = R.width * R.height;
-    const int pixel = (int)(gid % npix), s = R.spp_begin + (int)(gid / npix);
+    pixel = (int)(gid % npix);
+    s = R.spp_begin + (int)(gid / npix);
     uint32_t rnd[4];
     philox4x32_10((uint32_t)pixel, (uint32_t)s, 0u, 0u, R.k0, R.k1, rnd);
     const int x = pixel % R.width, y = pixel / R.width;
     const float sx = ((float)x + u01(rnd[0])) / (float)R.width * 2.f - 1.f;
     const float sy = 1.f - ((float)y + u01(rnd[1])) / (float)R.height * 2.f;
     const Camera& c = R.cam;
-    float dx = c.fx + sx * c.rx + sy * c.ux, dy = c.fy + sx * c.ry + sy * c.uy, dz = c.fz + sx * c.rz + sy * c.uz;
+    const float dx = c.fx + sx * c.rx + sy * c.ux, dy = c.fy + sx * c.ry + sy * c.uy, dz = c.fz + sx * c.rz + sy * c.uz;
     const float inv = rsqrtf(dx * dx + dy * dy + dz * dz);
-    P.org[i] = make_float4(c.px, c.py, c.pz, 0.f);
-    P.dir[i] = make_float4(dx * inv, dy * inv, dz * inv, 0.f);
-    P.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
-    P.rad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    P.pixel[i] = pixel; P.sample[i] = s;
-    P.mat[i] = -1;
+    o4 = make_float4(c.px, c.py, c.pz, 0.f);
+    d4 = make_float4(dx * inv, dy * inv, dz * inv, 0.f);
 }
 
 // BSDF-stage buffers of one pass (float4 AoS over `cap` slots)
@@ -197,33 +194,44 @@ struct StageBuf {
 };
 
 // ---- trace: intersect, terminate misses, prepare the BSDF-stage inputs ---------------------------
-// Live paths.  Depth 0 walks the pass's paths directly; from depth 1 on the kernels walk the list of
-// paths that the previous bounce's shade kernel continued (live_in[0 .. *nlive_in)), so every
-// per-bounce kernel costs in proportion to the paths still alive, not to the pass size.
+// Live paths.  Every per-bounce kernel walks a list of path indices, so it costs in proportion to the
+// paths still alive, not to the pass size: at depth 0 the list holds the camera rays that hit
+// something (appended by rt_primary_kernel), from depth 1 on the paths that the previous bounce's
+// shade kernel continued.
 struct LiveList {
-    const int* in;         // NULL at depth 0
+    const int* in;
     const int* count_in;
     int* out;              // written by rt_shade_kernel
     int* count_out;        // zeroed by rt_scan_kernel of the same bounce
 };
 
-__device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
+// Returns true when path i has a BSDF query this bounce.  PRIMARY: the camera ray is generated in
+// registers (depth 0) and path state is written only for the rays that hit a surface; a camera ray
+// that escapes costs one film update and no path-state traffic.
+template <bool PRIMARY>
+__device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
                                           const ClusterBox* clus, const int* smat, const int i, const int depth,
-                                          float4* __restrict__ film, unsigned long long* __restrict__ nquery) {
-    const int pixel = P.pixel[i];
-    const float4 dead = make_float4(0.f, 0.f, -1.f, 0.f);
-    if (pixel < 0) { P.mat[i] = -1; S.wi4[i] = dead; S.woe4[i] = dead; return; }
-    const float4 o4 = P.org[i], d4 = P.dir[i];
+                                          const int64_t first, float4* __restrict__ film,
+                                          unsigned long long* __restrict__ nquery) {
+    int pixel, smp;
+    float4 o4, d4;
+    if (PRIMARY) {
+        camera_ray(R, first + i, pixel, smp, o4, d4);
+    } else {
+        pixel = P.pixel[i];
+        if (pixel < 0) { P.mat[i] = -1; return false; }
+        o4 = P.org[i]; d4 = P.dir[i];
+    }
     const float ox = o4.x, oy = o4.y, oz = o4.z, dx = d4.x, dy = d4.y, dz = d4.z;
     float t;
     const int hit = intersect_spheres(sph, clus, R.nspheres, ox, oy, oz, dx, dy, dz, t);
     bool finish = false;
-    const float4 l4 = P.rad[i];
-    float lr = l4.x, lg = l4.y, lb = l4.z;
+    float lr = 0.f, lg = 0.f, lb = 0.f;
+    if (!PRIMARY) { const float4 l4 = P.rad[i]; lr = l4.x; lg = l4.y; lb = l4.z; }
     if (hit < 0) {
         // escaped: environment radiance, MIS against the emitter sample of the previous bounce
         const float w = depth == 0 ? 1.f : power_heuristic(o4.w, 0.0795774715f);
-        const float4 t4 = P.thr[i];
+        const float4 t4 = PRIMARY ? make_float4(1.f, 1.f, 1.f, 0.f) : P.thr[i];
         lr = fmaf(t4.x * R.env[0], w, lr); lg = fmaf(t4.y * R.env[1], w, lg); lb = fmaf(t4.z * R.env[2], w, lb);
         finish = true;
     } else if (depth >= R.max_depth) {
@@ -246,19 +254,20 @@ __device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P
     }
     if (finish) {
         film_add(film, pixel, lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
-        P.pixel[i] = -1; P.mat[i] = -1; S.wi4[i] = dead; S.woe4[i] = dead;
-        return;
+        if (!PRIMARY) { P.pixel[i] = -1; P.mat[i] = -1; }
+        return false;
     }
+    if (!PRIMARY) smp = P.sample[i];
     uint32_t re[4], rb[4];
-    philox4x32_10((uint32_t)pixel, (uint32_t)P.sample[i], (uint32_t)(2 * depth + 1), 0u, R.k0, R.k1, re);
-    philox4x32_10((uint32_t)pixel, (uint32_t)P.sample[i], (uint32_t)(2 * depth + 2), 0u, R.k0, R.k1, rb);
+    philox4x32_10((uint32_t)pixel, (uint32_t)smp, (uint32_t)(2 * depth + 1), 0u, R.k0, R.k1, re);
+    philox4x32_10((uint32_t)pixel, (uint32_t)smp, (uint32_t)(2 * depth + 2), 0u, R.k0, R.k1, rb);
     // emitter sampling: uniform direction on the sphere (constant environment), pdf 1/(4 pi)
     const float ez = 1.f - 2.f * u01(re[0]);
     const float er = sqrtf(fmaxf(0.f, 1.f - ez * ez));
     float es, ec;
     sincospif(2.f * u01(re[1]), &es, &ec);
     const float ex = er * ec, ey = er * es;
-    float4 woe = dead;
+    float4 woe = make_float4(0.f, 0.f, -1.f, 0.f);
     const float lz = ex * nx + ey * ny + ez * nz;
     if (lz > 0.f && !occluded(sph, clus, R.nspheres, fmaf(kRayEps, nx, hx), fmaf(kRayEps, ny, hy), fmaf(kRayEps, nz, hz), ex, ey, ez))
         woe = make_float4(ex * s[0] + ey * s[1] + ez * s[2], ex * tt[0] + ey * tt[1] + ez * tt[2], lz, 0.f);
@@ -267,14 +276,62 @@ __device__ __forceinline__ void trace_one(const RenderDev& R, const PathState& P
         const unsigned live = __activemask();
         if ((threadIdx.x & 31) == __ffs(live) - 1) atomicAdd(nquery, (unsigned long long)__popc(live));
     }
+    if (PRIMARY) {
+        P.pixel[i] = pixel; P.sample[i] = smp;
+        P.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+        P.rad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     P.nrm[i] = make_float4(nx, ny, nz, 0.f);
     P.hit[i] = make_float4(hx, hy, hz, 0.f);
     P.mat[i] = m;
     S.wi4[i] = make_float4(wix, wiy, wiz, (float)m);
     S.woe4[i] = woe;
     S.u4[i] = make_float4(u01(rb[0]), u01(rb[1]), u01(rb[2]), 0.f);
+    return true;
 }
 
+struct SceneSmem {
+    float4 sph[kMaxSpheres];
+    ClusterBox clus[kMaxClusters];
+    int smat[kMaxSpheres];
+};
+__device__ __forceinline__ void stage_scene(SceneSmem& sc, const int nspheres, const float4* __restrict__ spheres,
+                                            const ClusterBox* __restrict__ clusters, const int* __restrict__ sphere_mat) {
+    for (int s = threadIdx.x; s < nspheres; s += blockDim.x) { sc.sph[s] = spheres[s]; sc.smat[s] = sphere_mat[s]; }
+    for (int k = threadIdx.x; k * kClusterSize < nspheres; k += blockDim.x) sc.clus[k] = clusters[k];
+    __syncthreads();
+}
+
+// depth 0: camera ray + first intersection in one kernel, one thread per path of the pass; the
+// rays that hit are appended to the depth-0 live list (one atomic per warp)
+__global__ void __launch_bounds__(256) rt_primary_kernel(const RenderDev R, const PathState P, const StageBuf S,
+                                                         const float4* __restrict__ spheres,
+                                                         const ClusterBox* __restrict__ clusters,
+                                                         const int* __restrict__ sphere_mat,
+                                                         const PassInfo* __restrict__ pass, float4* __restrict__ film,
+                                                         unsigned long long* __restrict__ nquery, int* live_out,
+                                                         int* live_count) {
+    __shared__ SceneSmem sc;
+    const int np = pass->np;
+    const int64_t first = pass->first;
+    if (blockIdx.x * blockDim.x >= np) return;
+    stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat);
+    const int lane = threadIdx.x & 31;
+    for (int j0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); j0 < np; j0 += gridDim.x * blockDim.x) {
+        const int i = j0 + lane;
+        const bool q = i < np && trace_one<true>(R, P, S, sc.sph, sc.clus, sc.smat, i, 0, first, film, nquery);
+        const unsigned hits = __ballot_sync(0xffffffffu, q);
+        if (hits) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(live_count, __popc(hits));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            MERL_CHECK(base >= 0 && base + __popc(hits) <= np);
+            if (q) live_out[base + __popc(hits & ((1u << lane) - 1u))] = i;
+        }
+    }
+}
+
+// depth >= 1: the paths of the live list
 __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const PathState P, const StageBuf S,
                                                        const float4* __restrict__ spheres,
                                                        const ClusterBox* __restrict__ clusters,
@@ -282,19 +339,15 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
                                                        const PassInfo* __restrict__ pass, const int depth,
                                                        float4* __restrict__ film,
                                                        unsigned long long* __restrict__ nquery, const LiveList L) {
-    __shared__ float4 sph[kMaxSpheres];
-    __shared__ ClusterBox clus[kMaxClusters];
-    __shared__ int smat[kMaxSpheres];
-    const int count = L.in ? *L.count_in : pass->np;
+    __shared__ SceneSmem sc;
+    const int count = *L.count_in;
     if (blockIdx.x * blockDim.x >= count) return;          // whole CTA beyond the live range
-    for (int s = threadIdx.x; s < R.nspheres; s += blockDim.x) { sph[s] = spheres[s]; smat[s] = sphere_mat[s]; }
-    for (int k = threadIdx.x; k * kClusterSize < R.nspheres; k += blockDim.x) clus[k] = clusters[k];
-    __syncthreads();
+    stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat);
     MERL_CHECK(count >= 0 && count <= pass->np);
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
-        const int i = L.in ? L.in[j] : j;
+        const int i = L.in[j];
         MERL_CHECK(i >= 0 && i < pass->np);
-        trace_one(R, P, S, sph, clus, smat, i, depth, film, nquery);
+        trace_one<false>(R, P, S, sc.sph, sc.clus, sc.smat, i, depth, 0, film, nquery);
     }
 }
 
@@ -302,12 +355,12 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
 __global__ void rt_hist_kernel(const int* __restrict__ mat, const PassInfo* __restrict__ pass, const int ntables,
                                int* counts, const LiveList L) {
     extern __shared__ int h[];
-    const int count = L.in ? *L.count_in : pass->np;
+    const int count = *L.count_in;
     if (blockIdx.x * blockDim.x >= count) return;
     for (int k = threadIdx.x; k < ntables; k += blockDim.x) h[k] = 0;
     __syncthreads();
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
-        const int m = mat[L.in ? L.in[j] : j];
+        const int m = mat[L.in[j]];
         if (m >= 0) atomicAdd(&h[m], 1);
     }
     __syncthreads();
@@ -357,12 +410,12 @@ __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int nt
 }
 __global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B,
                                   const PassInfo* __restrict__ pass, int* cursor, const LiveList L) {
-    const int count = L.in ? *L.count_in : pass->np;
+    const int count = *L.count_in;
     const int lane = threadIdx.x & 31;
     // warp-uniform trip count: __match_any_sync needs the whole warp
     for (int j0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); j0 < count; j0 += gridDim.x * blockDim.x) {
         const int j = j0 + lane;
-        const int i = j < count ? (L.in ? L.in[j] : j) : -1;
+        const int i = j < count ? L.in[j] : -1;
         const int m = i >= 0 ? P.mat[i] : -1;
         // one atomic per (warp, material): neighbouring pixels mostly share a material
         const unsigned peers = __match_any_sync(0xffffffffu, m);
