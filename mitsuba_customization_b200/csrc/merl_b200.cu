@@ -1286,19 +1286,19 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         // depth 0: camera rays and their first intersection in one kernel over the whole pass; its
         // hits form the depth-0 live list.  Every other kernel walks a live list (grid-stride over
         // a grid that covers a few waves; CTAs beyond the live count exit at once).
-        rt_primary_kernel<<<nb, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_nq, d_live[0], d_nlive);
+        rt_primary_kernel<<<nb, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_live[0], d_nlive);
         const int g = std::min(nb, t0->num_sms * 16);
         for (int depth = 0; depth <= p->max_depth; ++depth) {
             const int cur = depth & 1, nxt = cur ^ 1;
             const LiveList L{d_live[cur], d_nlive + cur, d_live[nxt], d_nlive + nxt};
-            if (depth) rt_trace_kernel<<<g, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, d_nq, L);
+            if (depth) rt_trace_kernel<<<g, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, L);
             if (depth == p->max_depth) break;   // the last trace only collects escaped paths
             // live queries -> contiguous, material-sorted segments (with one table this is plain
             // stream compaction: the BSDF stage then touches live queries only)
             rt_hist_kernel<<<std::min(g, t0->num_sms * 4), 256, sizeof(int) * ntables, q>>>(P.mat, d_pass, ntables, d_counts, L);
             rt_scan_kernel<<<1, 1024, 0, q>>>(d_counts, ntables, d_seg, d_cursor, d_items, 4 * std::min(grid_e, grid_f),
-                                              d_nlive + nxt);
-            rt_scatter_kernel<<<g, 256, 0, q>>>(P, A, B, d_pass, d_cursor, L);
+                                              d_nlive + nxt, d_nq);
+            rt_scatter_kernel<<<g, 256, 2 * sizeof(int) * ntables, q>>>(P, A, B, d_pass, d_cursor, ntables, L);
             stream_multi_kernel<EvalPdfAosOp, 4 * kMinbScale><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, q>>>(
                 d_tabs, ntables, d_seg, d_items, EvalPdfAosOp{B.wi4, B.woe4, B.fe4}, img_e);
             stream_multi_kernel<SampleAosOp, 3 * kMinbScale><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, q>>>(

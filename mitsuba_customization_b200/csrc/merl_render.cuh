@@ -193,6 +193,35 @@ struct StageBuf {
     float4 *fe4, *wos4, *w4;        // outputs: (f cos, pdf_b) at woe; (wo, pdf) sampled; (weight, lobe)
 };
 
+// Appending to a list shared by the whole grid: one global atomic per CTA and iteration instead of
+// one per warp (with one counter for the whole grid the per-warp atomics serialise in L2 and the
+// kernels spend most of their time waiting for the returned offsets: profiles/r01_tuning.md §5).
+// Every thread of the CTA must call it (CTA-uniform control flow); returns the destination index of
+// the calling thread's element when `flag` is set.  s_warp: kAppendWarps ints of shared memory.
+constexpr int kAppendWarps = 8;   // 256-thread CTAs
+__device__ __forceinline__ int cta_append(const bool flag, int* counter, int* s_warp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned b = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s_warp[warp] = __popc(b);
+    __syncthreads();
+    if (warp == 0) {
+        const int c = lane < kAppendWarps ? s_warp[lane] : 0;
+        int inc = c;
+#pragma unroll
+        for (int o = 1; o < kAppendWarps; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, inc, kAppendWarps - 1);
+        int base = 0;
+        if (lane == 0 && total) base = atomicAdd(counter, total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (lane < kAppendWarps) s_warp[lane] = base + inc - c;
+    }
+    __syncthreads();
+    return s_warp[warp] + __popc(b & ((1u << lane) - 1u));
+}
+
 // ---- trace: intersect, terminate misses, prepare the BSDF-stage inputs ---------------------------
 // Live paths.  Every per-bounce kernel walks a list of path indices, so it costs in proportion to the
 // paths still alive, not to the pass size: at depth 0 the list holds the camera rays that hit
@@ -211,8 +240,7 @@ struct LiveList {
 template <bool PRIMARY>
 __device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
                                           const ClusterBox* clus, const int* smat, const int i, const int depth,
-                                          const int64_t first, float4* __restrict__ film,
-                                          unsigned long long* __restrict__ nquery) {
+                                          const int64_t first, float4* __restrict__ film) {
     int pixel, smp;
     float4 o4, d4;
     if (PRIMARY) {
@@ -272,10 +300,6 @@ __device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P
     if (lz > 0.f && !occluded(sph, clus, R.nspheres, fmaf(kRayEps, nx, hx), fmaf(kRayEps, ny, hy), fmaf(kRayEps, nz, hz), ex, ey, ez))
         woe = make_float4(ex * s[0] + ey * s[1] + ez * s[2], ex * tt[0] + ey * tt[1] + ez * tt[2], lz, 0.f);
     const int m = smat[hit];
-    {   // one counter update per warp: live BSDF queries of this bounce
-        const unsigned live = __activemask();
-        if ((threadIdx.x & 31) == __ffs(live) - 1) atomicAdd(nquery, (unsigned long long)__popc(live));
-    }
     if (PRIMARY) {
         P.pixel[i] = pixel; P.sample[i] = smp;
         P.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
@@ -303,31 +327,25 @@ __device__ __forceinline__ void stage_scene(SceneSmem& sc, const int nspheres, c
 }
 
 // depth 0: camera ray + first intersection in one kernel, one thread per path of the pass; the
-// rays that hit are appended to the depth-0 live list (one atomic per warp)
+// rays that hit are appended to the depth-0 live list (cta_append)
 __global__ void __launch_bounds__(256) rt_primary_kernel(const RenderDev R, const PathState P, const StageBuf S,
                                                          const float4* __restrict__ spheres,
                                                          const ClusterBox* __restrict__ clusters,
                                                          const int* __restrict__ sphere_mat,
                                                          const PassInfo* __restrict__ pass, float4* __restrict__ film,
-                                                         unsigned long long* __restrict__ nquery, int* live_out,
-                                                         int* live_count) {
+                                                         int* live_out, int* live_count) {
     __shared__ SceneSmem sc;
     const int np = pass->np;
     const int64_t first = pass->first;
     if (blockIdx.x * blockDim.x >= np) return;
     stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat);
-    const int lane = threadIdx.x & 31;
-    for (int j0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); j0 < np; j0 += gridDim.x * blockDim.x) {
-        const int i = j0 + lane;
-        const bool q = i < np && trace_one<true>(R, P, S, sc.sph, sc.clus, sc.smat, i, 0, first, film, nquery);
-        const unsigned hits = __ballot_sync(0xffffffffu, q);
-        if (hits) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(live_count, __popc(hits));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            MERL_CHECK(base >= 0 && base + __popc(hits) <= np);
-            if (q) live_out[base + __popc(hits & ((1u << lane) - 1u))] = i;
-        }
+    __shared__ int s_warp[kAppendWarps];
+    for (int j0 = blockIdx.x * blockDim.x; j0 < np; j0 += gridDim.x * blockDim.x) {   // CTA-uniform trip count
+        const int i = j0 + threadIdx.x;
+        const bool q = i < np && trace_one<true>(R, P, S, sc.sph, sc.clus, sc.smat, i, 0, first, film);
+        const int dst = cta_append(q, live_count, s_warp);
+        MERL_CHECK(!q || (dst >= 0 && dst < np));
+        if (q) live_out[dst] = i;
     }
 }
 
@@ -337,8 +355,7 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
                                                        const ClusterBox* __restrict__ clusters,
                                                        const int* __restrict__ sphere_mat,
                                                        const PassInfo* __restrict__ pass, const int depth,
-                                                       float4* __restrict__ film,
-                                                       unsigned long long* __restrict__ nquery, const LiveList L) {
+                                                       float4* __restrict__ film, const LiveList L) {
     __shared__ SceneSmem sc;
     const int count = *L.count_in;
     if (blockIdx.x * blockDim.x >= count) return;          // whole CTA beyond the live range
@@ -347,7 +364,7 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
         const int i = L.in[j];
         MERL_CHECK(i >= 0 && i < pass->np);
-        trace_one<false>(R, P, S, sc.sph, sc.clus, sc.smat, i, depth, 0, film, nquery);
+        trace_one<false>(R, P, S, sc.sph, sc.clus, sc.smat, i, depth, 0, film);
     }
 }
 
@@ -375,7 +392,8 @@ __global__ void rt_hist_kernel(const int* __restrict__ mat, const PassInfo* __re
 // few items and thin ones (late bounces) still spread over many CTAs instead of one CTA walking
 // many tables.
 __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int ntables, int* seg_off, int* cursor,
-                                                       int* item_off, const int target_items, int* next_live_count) {
+                                                       int* item_off, const int target_items, int* next_live_count,
+                                                       unsigned long long* __restrict__ nquery) {
     __shared__ int sc[1024];
     __shared__ int chunk_s;
     const int k = threadIdx.x;
@@ -395,6 +413,7 @@ __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int nt
     const int inc = scan(c);
     if (k < ntables) { seg_off[k] = inc - c; cursor[k] = inc - c; counts[k] = 0; }
     if (k == 1023) {
+        *nquery += (unsigned long long)sc[1023];   // statistics: BSDF queries of the whole render
         int ch = (sc[1023] + target_items - 1) / max(target_items, 1);
         ch = (ch + 31) & ~31;
         chunk_s = min(max(ch, 128), 8192);
@@ -408,26 +427,55 @@ __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int nt
     if (k < ntables) item_off[k] = iinc - items;
     if (k == ntables - 1) { item_off[ntables] = iinc; item_off[ntables + 1] = chunk; }
 }
-__global__ void rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B,
-                                  const PassInfo* __restrict__ pass, int* cursor, const LiveList L) {
+// Live queries -> their material's segment of the stage buffers.  A CTA takes kScatterPer * 256 list
+// entries per iteration, counts them per material in shared memory (one shared atomic per warp and
+// material: neighbouring pixels mostly share one), reserves each material's range with ONE global
+// atomic per CTA, and copies.  Dynamic shared memory: 2 * ntables ints.
+constexpr int kScatterPer = 4;
+__global__ void __launch_bounds__(256) rt_scatter_kernel(const PathState P, const StageBuf A, const StageBuf B,
+                                                         const PassInfo* __restrict__ pass, int* cursor,
+                                                         const int ntables, const LiveList L) {
+    extern __shared__ int sm_scatter[];
+    int* cnt = sm_scatter;
+    int* base = sm_scatter + ntables;
     const int count = *L.count_in;
     const int lane = threadIdx.x & 31;
-    // warp-uniform trip count: __match_any_sync needs the whole warp
-    for (int j0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); j0 < count; j0 += gridDim.x * blockDim.x) {
-        const int j = j0 + lane;
-        const int i = j < count ? L.in[j] : -1;
-        const int m = i >= 0 ? P.mat[i] : -1;
-        // one atomic per (warp, material): neighbouring pixels mostly share a material
-        const unsigned peers = __match_any_sync(0xffffffffu, m);
-        int base = 0;
-        const int leader = __ffs(peers) - 1;
-        if (m >= 0 && lane == leader) base = atomicAdd(&cursor[m], __popc(peers));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (m < 0) continue;
-        const int slot = base + __popc(peers & ((1u << lane) - 1u));
-        MERL_CHECK(slot >= 0 && slot < pass->np && m < 1024);
-        P.slot[slot] = i;
-        B.wi4[slot] = A.wi4[i]; B.woe4[slot] = A.woe4[i]; B.u4[slot] = A.u4[i];
+    const int tile = blockDim.x * kScatterPer;
+    if (blockIdx.x * tile >= count) return;
+    for (int k = threadIdx.x; k < ntables; k += blockDim.x) cnt[k] = 0;
+    __syncthreads();
+    for (int j0 = blockIdx.x * tile; j0 < count; j0 += gridDim.x * tile) {   // CTA-uniform trip count
+        int idx[kScatterPer], mat[kScatterPer], off[kScatterPer];
+#pragma unroll
+        for (int e = 0; e < kScatterPer; ++e) {
+            const int j = j0 + e * blockDim.x + threadIdx.x;
+            idx[e] = j < count ? L.in[j] : -1;
+        }
+#pragma unroll
+        for (int e = 0; e < kScatterPer; ++e) mat[e] = idx[e] >= 0 ? P.mat[idx[e]] : -1;
+#pragma unroll
+        for (int e = 0; e < kScatterPer; ++e) {
+            const unsigned peers = __match_any_sync(0xffffffffu, mat[e]);
+            const int leader = __ffs(peers) - 1;
+            int b = 0;
+            if (mat[e] >= 0 && lane == leader) b = atomicAdd(&cnt[mat[e]], __popc(peers));
+            b = __shfl_sync(0xffffffffu, b, leader);
+            off[e] = b + __popc(peers & ((1u << lane) - 1u));
+        }
+        __syncthreads();
+        for (int k = threadIdx.x; k < ntables; k += blockDim.x) {
+            const int c = cnt[k];
+            if (c) { base[k] = atomicAdd(&cursor[k], c); cnt[k] = 0; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < kScatterPer; ++e) {
+            if (mat[e] < 0) continue;
+            const int i = idx[e], slot = base[mat[e]] + off[e];
+            MERL_CHECK(slot >= 0 && slot < pass->np && mat[e] < ntables);
+            P.slot[slot] = i;
+            B.wi4[slot] = A.wi4[i]; B.woe4[slot] = A.woe4[i]; B.u4[slot] = A.u4[i];
+        }
     }
 }
 
@@ -436,14 +484,14 @@ __device__ __forceinline__ bool shade_one(const RenderDev& R, const PathState& P
                                           const int i, float4* __restrict__ film);
 
 // One thread per BSDF-stage slot (the live queries of this bounce, nq = seg_off[ntables]); paths
-// that continue are appended to the next bounce's live list, one atomic per warp.
+// that continue are appended to the next bounce's live list (cta_append).
 __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const PathState P, const StageBuf S,
                                                        const int* __restrict__ nq_ptr, float4* __restrict__ film,
                                                        const LiveList L) {
+    __shared__ int s_warp[kAppendWarps];
     const int nq = *nq_ptr;
-    const int lane = threadIdx.x & 31;
-    for (int s0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); s0 < nq; s0 += gridDim.x * blockDim.x) {
-        const int slot = s0 + lane;
+    for (int s0 = blockIdx.x * blockDim.x; s0 < nq; s0 += gridDim.x * blockDim.x) {   // CTA-uniform trip count
+        const int slot = s0 + threadIdx.x;
         int i = -1;
         bool go = false;
         if (slot < nq) {
@@ -451,14 +499,9 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
             MERL_CHECK(i >= 0 && P.pixel[i] >= 0 && P.pixel[i] < R.width * R.height);
             go = shade_one(R, P, S, slot, i, film);
         }
-        const unsigned cont = __ballot_sync(0xffffffffu, go);
-        if (cont) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(L.count_out, __popc(cont));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            MERL_CHECK(base >= 0 && base + __popc(cont) <= nq);
-            if (go) L.out[base + __popc(cont & ((1u << lane) - 1u))] = i;
-        }
+        const int dst = cta_append(go, L.count_out, s_warp);
+        MERL_CHECK(!go || (dst >= 0 && dst < nq));
+        if (go) L.out[dst] = i;
     }
 }
 
