@@ -1276,7 +1276,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     RT_TRY(cudaMemcpyAsync(d_pass, &pass0, sizeof pass0, cudaMemcpyHostToDevice, s));
     const int64_t npasses = (total + cap - 1) / cap;
     const int nb = (int)((cap + 255) / 256);
-    // One wavefront pass = 2 + 7 max_depth launches, most of them over a handful of live paths at
+    // One wavefront pass = 2 + 6 max_depth launches, most of them over a handful of live paths at
     // the later bounces: launch-latency bound when enqueued one by one.  The pass is recorded once
     // as a CUDA graph (it reads its sample range from d_pass, advanced by its last node) and
     // replayed npasses times.  Capture needs a non-legacy stream, so the work runs on a side
@@ -1286,16 +1286,15 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         // depth 0: camera rays and their first intersection in one kernel over the whole pass; its
         // hits form the depth-0 live list.  Every other kernel walks a live list (grid-stride over
         // a grid that covers a few waves; CTAs beyond the live count exit at once).
-        rt_primary_kernel<<<nb, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_live[0], d_nlive);
+        rt_primary_kernel<<<nb, 256, sizeof(int) * ntables, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_live[0], d_nlive, d_counts);
         const int g = std::min(nb, t0->num_sms * 16);
         for (int depth = 0; depth <= p->max_depth; ++depth) {
             const int cur = depth & 1, nxt = cur ^ 1;
             const LiveList L{d_live[cur], d_nlive + cur, d_live[nxt], d_nlive + nxt};
-            if (depth) rt_trace_kernel<<<g, 256, 0, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, L);
+            if (depth) rt_trace_kernel<<<g, 256, sizeof(int) * ntables, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, depth, film, L, d_counts);
             if (depth == p->max_depth) break;   // the last trace only collects escaped paths
             // live queries -> contiguous, material-sorted segments (with one table this is plain
             // stream compaction: the BSDF stage then touches live queries only)
-            rt_hist_kernel<<<std::min(g, t0->num_sms * 4), 256, sizeof(int) * ntables, q>>>(P.mat, d_pass, ntables, d_counts, L);
             rt_scan_kernel<<<1, 1024, 0, q>>>(d_counts, ntables, d_seg, d_cursor, d_items, 4 * std::min(grid_e, grid_f),
                                               d_nlive + nxt, d_nq);
             rt_scatter_kernel<<<g, 256, 2 * sizeof(int) * ntables, q>>>(P, A, B, d_pass, d_cursor, ntables, L);
@@ -1307,7 +1306,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         }
         rt_advance_kernel<<<1, 1, 0, q>>>(d_pass, (long long)total, (int)cap, d_nlive);
     };
-    const int64_t per_pass = 2 + 7 * (int64_t)p->max_depth;
+    const int64_t per_pass = 2 + 6 * (int64_t)p->max_depth;
     // (a caller that is itself capturing `stream` gets the plain launches: they become part of its graph)
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) { cudaGetLastError(); cap_status = cudaStreamCaptureStatusNone; }

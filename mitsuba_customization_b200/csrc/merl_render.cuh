@@ -240,7 +240,7 @@ struct LiveList {
 template <bool PRIMARY>
 __device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
                                           const ClusterBox* clus, const int* smat, const int i, const int depth,
-                                          const int64_t first, float4* __restrict__ film) {
+                                          const int64_t first, float4* __restrict__ film, int* hist) {
     int pixel, smp;
     float4 o4, d4;
     if (PRIMARY) {
@@ -300,6 +300,11 @@ __device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P
     if (lz > 0.f && !occluded(sph, clus, R.nspheres, fmaf(kRayEps, nx, hx), fmaf(kRayEps, ny, hy), fmaf(kRayEps, nz, hz), ex, ey, ez))
         woe = make_float4(ex * s[0] + ey * s[1] + ez * s[2], ex * tt[0] + ey * tt[1] + ez * tt[2], lz, 0.f);
     const int m = smat[hit];
+    {   // this bounce's queries per material, for the counting sort: one shared atomic per group of
+        // converged lanes with the same material
+        const unsigned peers = __match_any_sync(__activemask(), m);
+        if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[m], __popc(peers));
+    }
     if (PRIMARY) {
         P.pixel[i] = pixel; P.sample[i] = smp;
         P.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
@@ -320,10 +325,18 @@ struct SceneSmem {
     int smat[kMaxSpheres];
 };
 __device__ __forceinline__ void stage_scene(SceneSmem& sc, const int nspheres, const float4* __restrict__ spheres,
-                                            const ClusterBox* __restrict__ clusters, const int* __restrict__ sphere_mat) {
+                                            const ClusterBox* __restrict__ clusters, const int* __restrict__ sphere_mat,
+                                            int* hist, const int ntables) {
+    for (int k = threadIdx.x; k < ntables; k += blockDim.x) hist[k] = 0;
     for (int s = threadIdx.x; s < nspheres; s += blockDim.x) { sc.sph[s] = spheres[s]; sc.smat[s] = sphere_mat[s]; }
     for (int k = threadIdx.x; k * kClusterSize < nspheres; k += blockDim.x) sc.clus[k] = clusters[k];
     __syncthreads();
+}
+// the CTA's per-material query counts -> the global histogram the scan kernel turns into segments
+__device__ __forceinline__ void flush_hist(const int* hist, const int ntables, int* __restrict__ counts) {
+    __syncthreads();
+    for (int k = threadIdx.x; k < ntables; k += blockDim.x)
+        if (hist[k]) atomicAdd(&counts[k], hist[k]);
 }
 
 // depth 0: camera ray + first intersection in one kernel, one thread per path of the pass; the
@@ -333,20 +346,22 @@ __global__ void __launch_bounds__(256) rt_primary_kernel(const RenderDev R, cons
                                                          const ClusterBox* __restrict__ clusters,
                                                          const int* __restrict__ sphere_mat,
                                                          const PassInfo* __restrict__ pass, float4* __restrict__ film,
-                                                         int* live_out, int* live_count) {
+                                                         int* live_out, int* live_count, int* __restrict__ counts) {
+    extern __shared__ int hist[];   // R.ntables ints
     __shared__ SceneSmem sc;
     const int np = pass->np;
     const int64_t first = pass->first;
     if (blockIdx.x * blockDim.x >= np) return;
-    stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat);
+    stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat, hist, R.ntables);
     __shared__ int s_warp[kAppendWarps];
     for (int j0 = blockIdx.x * blockDim.x; j0 < np; j0 += gridDim.x * blockDim.x) {   // CTA-uniform trip count
         const int i = j0 + threadIdx.x;
-        const bool q = i < np && trace_one<true>(R, P, S, sc.sph, sc.clus, sc.smat, i, 0, first, film);
+        const bool q = i < np && trace_one<true>(R, P, S, sc.sph, sc.clus, sc.smat, i, 0, first, film, hist);
         const int dst = cta_append(q, live_count, s_warp);
         MERL_CHECK(!q || (dst >= 0 && dst < np));
         if (q) live_out[dst] = i;
     }
+    flush_hist(hist, R.ntables, counts);
 }
 
 // depth >= 1: the paths of the live list
@@ -355,35 +370,23 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
                                                        const ClusterBox* __restrict__ clusters,
                                                        const int* __restrict__ sphere_mat,
                                                        const PassInfo* __restrict__ pass, const int depth,
-                                                       float4* __restrict__ film, const LiveList L) {
+                                                       float4* __restrict__ film, const LiveList L,
+                                                       int* __restrict__ counts) {
+    extern __shared__ int hist[];   // R.ntables ints
     __shared__ SceneSmem sc;
     const int count = *L.count_in;
     if (blockIdx.x * blockDim.x >= count) return;          // whole CTA beyond the live range
-    stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat);
+    stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat, hist, R.ntables);
     MERL_CHECK(count >= 0 && count <= pass->np);
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
         const int i = L.in[j];
         MERL_CHECK(i >= 0 && i < pass->np);
-        trace_one<false>(R, P, S, sc.sph, sc.clus, sc.smat, i, depth, 0, film);
+        trace_one<false>(R, P, S, sc.sph, sc.clus, sc.smat, i, depth, 0, film, hist);
     }
+    flush_hist(hist, R.ntables, counts);
 }
 
 // ---- counting sort of the live queries by material (multi-material scenes) -----------------------
-__global__ void rt_hist_kernel(const int* __restrict__ mat, const PassInfo* __restrict__ pass, const int ntables,
-                               int* counts, const LiveList L) {
-    extern __shared__ int h[];
-    const int count = *L.count_in;
-    if (blockIdx.x * blockDim.x >= count) return;
-    for (int k = threadIdx.x; k < ntables; k += blockDim.x) h[k] = 0;
-    __syncthreads();
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
-        const int m = mat[L.in[j]];
-        if (m >= 0) atomicAdd(&h[m], 1);
-    }
-    __syncthreads();
-    for (int k = threadIdx.x; k < ntables; k += blockDim.x)
-        if (h[k]) atomicAdd(&counts[k], h[k]);
-}
 // One CTA of 1024 threads (ntables <= 1024), Hillis-Steele scans in shared memory:
 //   seg_off[0..ntables]   exclusive scan of counts (cursor = copy; counts cleared for the next bounce)
 //   item_off[0..ntables]  exclusive scan of ceil(count / chunk): the BSDF stage's work items, each at
