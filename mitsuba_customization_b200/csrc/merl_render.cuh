@@ -2,14 +2,17 @@
 //
 // The callers either side of the hot path, so that BASELINE configs 2 (one sphere, one table) and
 // 5 (many spheres, many tables) can be rendered and checked as images.  Headless: analytic
-// spheres, constant environment, pinhole camera, no graphics API.  Per bounce:
-//   rt_trace_kernel    intersect, terminate misses into the film, build the local frame, draw the
-//                      emitter direction + shadow ray, write the BSDF-stage inputs (float4 AoS)
-//   rt_sort_*          multi-material scenes only: counting sort of the live paths by material so
-//                      that each table's queries are one contiguous segment
+// spheres, constant environment, pinhole camera, no graphics API.  One wavefront pass:
+//   rt_primary_kernel  depth 0: camera ray + first intersection for every path of the pass; escaped
+//                      rays go straight to the film, the hits form the first live list
+//   rt_trace_kernel    depth >= 1, over the live list: intersect, terminate misses into the film
+//   (both)             build the local frame, draw the emitter direction + shadow ray, write the
+//                      BSDF-stage inputs (float4 AoS), count the queries per material
+//   rt_scan_kernel /   counting sort of the live queries by material, so that each table's queries
+//   rt_scatter_kernel  are one contiguous segment (one table: plain stream compaction)
 //   BSDF stage         EvalPdfAosOp + SampleAosOp (the kernels of the C ABI's *_aos entry points),
 //                      one launch pair per bounce; segmented over tables when there are several
-//   rt_shade_kernel    MIS-weighted emitter contribution, throughput update, next ray
+//   rt_shade_kernel    MIS-weighted emitter contribution, throughput update, next ray, next live list
 // The CPU oracle restates the same algorithm for the tests.  Included once, by merl_b200.cu.
 #pragma once
 #include "merl_kernels.cuh"
