@@ -93,6 +93,12 @@ int merl_table_set_cdf(merl_table_t* t, const float* cdf_host);
  * differentiable parameter): rebuild the sampler CDF rows and densities from it, asynchronously
  * on `stream`.  Mitsuba 3: parameters_changed({"data"}). */
 int merl_table_refresh_sampler(merl_table_t* t, merl_stream_t stream);
+/* The same when the new values live in ANOTHER device buffer (float4[ncell], same layout as
+ * d_cells): Dr.Jit optimisers replace a parameter array instead of writing into it, so the
+ * Mitsuba 3 host's parameters_changed({"data"}) hands the new array here.  Device-to-device copy
+ * into d_cells (skipped when cells4_device == d_cells), then the sampler refresh; asynchronous
+ * on `stream`. */
+int merl_table_update_cells(merl_table_t* t, const void* cells4_device, merl_stream_t stream);
 /* Copy tables back to the host; any pointer may be NULL.  Synchronous. */
 int merl_table_download(const merl_table_t* t, float* cells4_host, float* cdf_host, float* dens_host);
 
@@ -145,6 +151,11 @@ int merl_backward(const merl_table_t* t, const float* wix, const float* wiy, con
                   const float* wox, const float* woy, const float* woz, const float* gr,
                   const float* gg, const float* gb, const uint8_t* active, int64_t n,
                   float* grad_cells4, uint32_t flags, merl_stream_t stream);
+
+/* Zero the hit-count lane (.w) of a gradient table, leaving the pure gradient of the float4 cells
+ * (the .w lane of the table holds validity bits, which an optimiser must not move): what the
+ * Mitsuba 3 host's dr::CustomOp hands back to Dr.Jit.  Asynchronous on `stream`. */
+int merl_grad_clear_counts(const merl_table_t* t, float* grad_cells4, merl_stream_t stream);
 
 /* ---- AoS entry points for the Mitsuba 0.6 wavefront BSDF stage --------------------------
  * wi4 / wo4: float4 per query (xyz, w ignored).  out4 = (r, g, b, pdf). */

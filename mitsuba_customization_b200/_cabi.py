@@ -16,6 +16,8 @@ SYMBOLS = [
     "merl_table_params_default", "merl_table_create_from_file", "merl_table_create_from_host",
     "merl_table_destroy", "merl_table_info", "merl_table_set_cdf", "merl_table_download",
     "merl_table_refresh_sampler",
+    "merl_table_update_cells",
+    "merl_grad_clear_counts",
     "merl_file_report", "merl_table_save_packed", "merl_table_create_from_packed",
     "merl_bins", "merl_eval", "merl_pdf", "merl_eval_pdf", "merl_sample", "merl_backward",
     "merl_eval_pdf_aos", "merl_sample_aos", "merl_eval_pdf_host", "merl_sample_host",
@@ -83,6 +85,8 @@ def lib():
         L.merl_table_set_cdf.argtypes = [vp, vp]
         L.merl_table_download.argtypes = [vp, vp, vp, vp]
         L.merl_table_refresh_sampler.argtypes = [vp, vp]
+        L.merl_table_update_cells.argtypes = [vp, vp, vp]
+        L.merl_grad_clear_counts.argtypes = [vp, vp, vp]
         L.merl_file_report.argtypes = [C.c_char_p, C.POINTER(FileReport)]
         L.merl_table_save_packed.argtypes = [vp, C.c_char_p]
         L.merl_table_create_from_packed.argtypes = [C.c_char_p, i32, C.POINTER(vp)]

@@ -179,10 +179,18 @@ class MERL:
         """Differentiable parameters, as `traverse(TraversalCallback*)` would expose them."""
         return {"data": self.cells()}
 
-    def parameters_changed(self, keys=()):
-        """After `data` (cells()) was updated in place, e.g. by an optimiser step: rebuild the sampler."""
+    def parameters_changed(self, keys=(), data=None):
+        """After `data` (cells()) was updated in place, e.g. by an optimiser step: rebuild the sampler.
+        `data`: the new values in another (ncell, 4) float32 CUDA tensor (an optimiser that replaces
+        the parameter instead of writing into it); copied into the table first."""
         if not keys or "data" in keys:
-            check(_cabi.lib().merl_table_refresh_sampler(self._h, _stream(self.device)))
+            if data is not None:
+                if data.dtype != torch.float32 or tuple(data.shape) != (self.info.ncell, 4) or not data.is_cuda:
+                    raise ValueError("data must be a float32 CUDA tensor of shape (ncell, 4)")
+                data = data.contiguous()
+                check(_cabi.lib().merl_table_update_cells(self._h, C.c_void_p(data.data_ptr()), _stream(self.device)))
+            else:
+                check(_cabi.lib().merl_table_refresh_sampler(self._h, _stream(self.device)))
 
     def cells(self) -> torch.Tensor:
         """The prescaled float4 table on the device, (ncell, 4), zero-copy."""

@@ -548,6 +548,17 @@ extern "C" int merl_table_refresh_sampler(merl_table_t* t, merl_stream_t stream)
     return upload_sampler(t, nullptr, (cudaStream_t)stream);
 }
 
+// The optimiser's copy of the parameter -> the table the kernels read (Dr.Jit replaces parameter
+// arrays rather than writing into them), then what depends on it.
+extern "C" int merl_table_update_cells(merl_table_t* t, const void* cells4_device, merl_stream_t stream) {
+    if (!t || !cells4_device) return fail(MERL_ERR_ARG, "NULL argument");
+    DeviceGuard g(t->device);
+    if (cells4_device != (const void*)t->d_cells)
+        CUDA_TRY(cudaMemcpyAsync(t->d_cells, cells4_device, sizeof(float4) * t->ncell, cudaMemcpyDeviceToDevice,
+                                 (cudaStream_t)stream));
+    return upload_sampler(t, nullptr, (cudaStream_t)stream);
+}
+
 extern "C" int merl_table_download(const merl_table_t* t, float* cells4, float* cdf, float* dens) {
     if (!t) return fail(MERL_ERR_ARG, "NULL argument");
     DeviceGuard g(t->device);
@@ -813,6 +824,21 @@ extern "C" int merl_backward(const merl_table_t* t, const float* wix, const floa
     cudaStream_t s = (cudaStream_t)stream;
     if (flags & MERL_BWD_WARP_AGGREGATE) return gather ? run_backward<1, 1>(t, in, n, grad, s) : run_backward<1, 0>(t, in, n, grad, s);
     return gather ? run_backward<0, 1>(t, in, n, grad, s) : run_backward<0, 0>(t, in, n, grad, s);
+}
+
+// hit counts out of a gradient table
+static __global__ void grad_clear_counts_kernel(float4* __restrict__ grad, const int64_t ncell) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ncell; i += (int64_t)gridDim.x * blockDim.x)
+        grad[i].w = 0.f;
+}
+extern "C" int merl_grad_clear_counts(const merl_table_t* t, float* grad_cells4, merl_stream_t stream) {
+    if (!t || !grad_cells4) return fail(MERL_ERR_ARG, "NULL argument");
+    if ((uintptr_t)grad_cells4 & 15) return fail(MERL_ERR_ARG, "grad_cells4 must be 16-byte aligned");
+    DeviceGuard g(t->device);
+    grad_clear_counts_kernel<<<t->num_sms * 4, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(grad_cells4), t->ncell);
+    g_launches.fetch_add(1);
+    CUDA_TRY(cudaGetLastError());
+    return MERL_OK;
 }
 
 extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const float* wo4, int64_t n, float* out4,

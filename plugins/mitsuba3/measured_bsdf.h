@@ -17,11 +17,15 @@
 #include <mitsuba/core/properties.h>
 #include <mitsuba/render/bsdf.h>
 
+#include <drjit/custom.h>
+
 #include <algorithm>
 
 #include "../common/merl_host.h"
 
 NAMESPACE_BEGIN(mitsuba)
+
+template <typename Float, typename Spectrum> struct MerlEvalOp;   // merl_eval_op.h (end of this file)
 
 template <typename Float, typename Spectrum> class MeasuredBSDF : public BSDF<Float, Spectrum> {
 public:
@@ -40,6 +44,9 @@ public:
         check(merl_table_create_from_file(m_filename.c_str(), &params, m_device, m_table.put()),
               "loading the table");
         m_info = m_table.info();
+        // the differentiable parameter: the library's float4 table seen as a flat Float (no copy)
+        if constexpr (dr::is_cuda_v<Float>)
+            m_data = dr::map<Float>(const_cast<void*>(m_info.d_cells), (size_t) (4 * m_info.ncell));
         m_flags = BSDFFlags::GlossyReflection | BSDFFlags::FrontSide;
         m_components.push_back(m_flags);
     }
@@ -50,7 +57,22 @@ public:
         MI_MASKED_FUNCTION(ProfilerPhase::BSDFEvaluate, active_);
         if (!ctx.is_enabled(BSDFFlags::GlossyReflection)) return Spectrum(0.f);
         if constexpr (dr::is_cuda_v<Float>) {
-            Vector3f wi = si.wi, wo = wo_;
+            // *_ad_* variants: when `data` carries gradients the evaluation enters the AD graph as
+            // one custom operation whose adjoint is the scatter kernel (merl_eval_op.h)
+            if constexpr (dr::is_diff_v<Float>) {
+                if (dr::grad_enabled(m_data))
+                    return dr::custom<MerlEvalOp<Float, Spectrum>>(this, m_data, si.wi, wo_, active_);
+            }
+            return eval_primal(si.wi, wo_, active_);
+        } else {
+            return eval_pdf_packet(si.wi, wo_, active_).first;
+        }
+    }
+
+    // The kernel call itself, on detached operands (cuda variants only).
+    Spectrum eval_primal(const Vector3f& wi_, const Vector3f& wo_, Mask active_) const {
+        if constexpr (dr::is_cuda_v<Float>) {
+            Vector3f wi = wi_, wo = wo_;
             Mask active = active_;
             const size_t n = materialise(wi, wo, active);
             Float r = dr::empty<Float>(n), g = dr::empty<Float>(n), b = dr::empty<Float>(n);
@@ -60,7 +82,7 @@ public:
                   "eval");
             return Spectrum(r, g, b);
         } else {
-            return eval_pdf_packet(si.wi, wo_, active_).first;
+            Throw("%s: eval_primal is the cuda variants' path", m_plugin);
         }
     }
 
@@ -158,23 +180,45 @@ public:
     }
 
     // ---- differentiable parameter ----------------------------------------------------------
-    // `data` is the prescaled float4 table on the device.  In *_ad_* variants Dr.Jit would derive
-    // the adjoint of the gather itself; with an external kernel it is wired by hand: the
-    // dr::CustomOp in INTEGRATION.md §2 calls backward_table() from its backward().
+    // `data` is the prescaled float4 table on the device, exposed as a flat Float of 4 * ncell
+    // entries (r, g, b, validity bits per cell).  In *_ad_* variants Dr.Jit would derive the
+    // adjoint of a dr::gather itself; with an external kernel it is wired by hand: eval() enters
+    // the AD graph through MerlEvalOp, whose backward() calls backward_table().
     void traverse(TraversalCallback* cb) override {
-        cb->put_parameter("data", m_info.d_cells, +ParamFlags::Differentiable);
+        if constexpr (dr::is_cuda_v<Float>)
+            cb->put_parameter("data", m_data, +ParamFlags::Differentiable);
+        else
+            cb->put_parameter("data", m_info.d_cells, +ParamFlags::NonDifferentiable);
     }
 
+    // An optimiser step replaces m_data by a new array (Dr.Jit arrays are immutable values): its
+    // contents go back into the table the kernels read, then the sampler is rebuilt from it.
     void parameters_changed(const std::vector<std::string>& keys = {}) override {
-        if (keys.empty() || std::find(keys.begin(), keys.end(), "data") != keys.end())
+        if (!keys.empty() && std::find(keys.begin(), keys.end(), "data") == keys.end()) return;
+        if constexpr (dr::is_cuda_v<Float>) {
+            if (dr::width(m_data) != (size_t) (4 * m_info.ncell))
+                Throw("%s: parameter \"data\" must keep its %zu entries (got %zu)", m_plugin,
+                      (size_t) (4 * m_info.ncell), dr::width(m_data));
+            dr::eval(m_data);
+            check(merl_table_update_cells(m_table.get(), dr::detach(m_data).data(), jit_cuda_stream()),
+                  "updating the table");
+        } else {
             check(merl_table_refresh_sampler(m_table.get(), jit_cuda_stream()), "rebuilding the sampler");
+        }
     }
+
+    const Float& data() const { return m_data; }
+    Float& data() { return m_data; }
 
     // grad_cells4: device float4[ncell] (zeroed by the caller) += d eval / d data . grad_out.
     void backward_table(const SurfaceInteraction3f& si, const Vector3f& wo_, const Spectrum& grad_out_,
                         Mask active_, float* grad_cells4, bool warp_aggregate = true) const {
+        backward_table(si.wi, wo_, grad_out_, active_, grad_cells4, warp_aggregate);
+    }
+    void backward_table(const Vector3f& wi_, const Vector3f& wo_, const Spectrum& grad_out_, Mask active_,
+                        float* grad_cells4, bool warp_aggregate = true) const {
         if constexpr (dr::is_cuda_v<Float>) {
-            Vector3f wi = si.wi, wo = wo_;
+            Vector3f wi = wi_, wo = wo_;
             Spectrum go = grad_out_;
             Mask active = active_;
             const size_t n = materialise(wi, wo, active);
@@ -188,6 +232,12 @@ public:
         } else {
             Throw("%s: the table gradient needs a cuda_ad_* variant", m_plugin);
         }
+    }
+
+    // backward_table() leaves the number of queries per cell in the .w lane; a gradient of `data`
+    // must be zero there (that lane of the table holds validity bits).
+    void clear_hit_counts(float* grad_cells4) const {
+        check(merl_grad_clear_counts(m_table.get(), grad_cells4, jit_cuda_stream()), "clearing the hit counts");
     }
 
     std::string to_string() const override {
@@ -239,7 +289,10 @@ protected:
     int m_device = 0;
     merl_host::Table m_table;
     merl_table_info_t m_info{};
+    Float m_data;                    // cuda variants: view of the table (or the optimiser's replacement)
     mutable UInt32 m_last_lobe;
 };
 
 NAMESPACE_END(mitsuba)
+
+#include "merl_eval_op.h"

@@ -45,6 +45,13 @@ template <typename T> struct CUDAArray {
         mock_cuda_check(cudaMemcpy(a.data(), host, n * sizeof(T), cudaMemcpyHostToDevice), "cudaMemcpy H2D");
         return a;
     }
+    // dr::map<A>(ptr, n): an array over memory owned by someone else (upstream jit_var_mem_map)
+    static CUDAArray map_(void* device_ptr, size_t n) {
+        CUDAArray a;
+        a.n = n;
+        a.buf = std::shared_ptr<void>(device_ptr, [](void*) {});
+        return a;
+    }
     void store_(void* host) const {
         mock_cuda_check(cudaMemcpy(host, data(), n * sizeof(T), cudaMemcpyDeviceToHost), "cudaMemcpy D2H");
     }
@@ -79,6 +86,9 @@ template <typename A, typename V> A full(V v, size_t n = 1) {
     if constexpr (is_cuda_v<A>) return A::full_((typename A::Value) v, n); else return A(v);
 }
 template <typename A> A load(const void* host, size_t n) { return A::load_(host, n); }
+template <typename A> A map(void* device_ptr, size_t n) { return A::map_(device_ptr, n); }
+template <typename... Ts> bool grad_enabled(const Ts&...) { return false; }   // no AD in the mock
+template <typename A> const A& detach(const A& a) { return a; }
 template <typename A> void store(void* host, const A& a) { a.store_(host); }
 
 template <typename A> size_t width(const A& a) {

@@ -8,61 +8,17 @@
 //   out.bin    : float32 rgb[3][n], pdf[n], eval_only[3][n], pdf_only[n],
 //                s_wo[3][n], s_pdf[n], s_weight[3][n], uint32 s_lobe[n]      (cuda variant, all n)
 //                then the same block for the first min(n, 64) queries through the scalar variant
-#include "../mitsuba3/merl.cpp"
-#include "../mitsuba3/customized_measurment.cpp"
-
-#include <cstdlib>
-#include <fstream>
-#include <iostream>
-
-using namespace mitsuba;
-using FloatC = dr::CUDAArray<float>;
-using SpectrumC = Vector<FloatC, 3>;
-using SpectrumS = Vector<float, 3>;
-
-template <typename T> static std::vector<T> read_vec(std::ifstream& f, size_t n) {
-    std::vector<T> v(n);
-    f.read(reinterpret_cast<char*>(v.data()), (std::streamsize) (n * sizeof(T)));
-    if (!f) throw std::runtime_error("short read");
-    return v;
-}
-template <typename T> static void write_vec(std::ofstream& f, const std::vector<T>& v) {
-    f.write(reinterpret_cast<const char*>(v.data()), (std::streamsize) (v.size() * sizeof(T)));
-}
-static std::vector<float> to_host(const FloatC& a) {
-    std::vector<float> h(a.size());
-    dr::store(h.data(), a);
-    return h;
-}
-
-template <typename F, typename S> static std::unique_ptr<BSDF<F, S>> make(const std::string& kind, const Properties& p) {
-    if (kind == "merl") return std::make_unique<MERL<F, S>>(p);
-    if (kind == "customized_measurment") return std::make_unique<CustomizedMeasurment<F, S>>(p);
-    Throw("unknown plugin \"%s\"", kind.c_str());
-}
+#include "m3_test_common.h"
 
 int main(int argc, char** argv) {
     if (argc < 5) { std::cerr << "usage: m3_host_test plugin table queries out [key=value ...]\n"; return 2; }
     try {
         const std::string kind = argv[1];
-        Properties props;
-        props.set_string("filename", argv[2]);
-        for (int i = 5; i < argc; ++i) {
-            const std::string kv = argv[i];
-            const size_t eq = kv.find('=');
-            if (eq == std::string::npos) Throw("bad parameter \"%s\"", kv.c_str());
-            const std::string k = kv.substr(0, eq), v = kv.substr(eq + 1);
-            char* end = nullptr;
-            const double d = std::strtod(v.c_str(), &end);
-            if (end && *end == 0 && !v.empty()) props.set_float(k, d); else props.set_string(k, v);
-        }
-        std::ifstream fq(argv[3], std::ios::binary);
-        int64_t n = 0;
-        fq.read(reinterpret_cast<char*>(&n), 8);
-        if (!fq || n < 0) Throw("cannot read %s", argv[3]);
-        const auto wi = read_vec<float>(fq, 3 * n), wo = read_vec<float>(fq, 3 * n), u1 = read_vec<float>(fq, n),
-                   u2 = read_vec<float>(fq, 2 * n);
-        const auto act = read_vec<uint8_t>(fq, n);
+        const Properties props = parse_props(argv[2], argc, argv, 5);
+        const Queries Q(argv[3]);
+        const int64_t n = Q.n;
+        const auto &wi = Q.wi, &wo = Q.wo, &u1 = Q.u1, &u2 = Q.u2;
+        const auto& act = Q.act;
         std::ofstream fo(argv[4], std::ios::binary);
 
         BSDFContext ctx;
