@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--log2-batch", type=int, default=LOG2_BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--no-render", action="store_true", help="skip the render legs of the extras")
+    ap.add_argument("--render-tables", type=int, default=100, help="tables of render config 5 (0 = skip it)")
     return ap.parse_args()
 
 
@@ -320,6 +322,7 @@ def run_b200(args):
         grad = torch.zeros(plug.info.ncell, 4, device=dev)
         ms_b, _ = timed(lambda: plug.backward(si, wo, g, grad_cells=grad), k, 3)
         extras["backward_gquery_s_no_allreduce"] = world * n / (ms_b / k * 1e-3) / 1e9
+        comm = None
         if world > 1:
             from mitsuba_customization_b200 import distributed as D
             comm = D.Comm(rank, world, local)   # libmerl_b200's NCCL communicator (id shipped over torch.distributed)
@@ -344,9 +347,18 @@ def run_b200(args):
             ms_bs, _ = timed(bwd_strong, k, 3)
             extras["backward_2p26_total_ms_with_allreduce"] = ms_bs / k
             extras["backward_2p26_total_gquery_s"] = (1 << 26) / (ms_bs / k * 1e-3) / 1e9
-            comm.close()
             del sw, swo, sg
         del g, grad
+        # BASELINE configs 2 and 5 (the metric's spp*Mpix/s @ 1/2/4/8): the wavefront harness around the
+        # BSDF stage; every rank renders its share of the sample indices, films summed with one allreduce.
+        # A failure here is reported in the line, it never takes the headline down.
+        if not args.no_render:
+            try:
+                extras["render"] = render_legs(plug, world, rank, local, comm, timed, args.render_tables)
+            except Exception as e:  # noqa: BLE001
+                extras["render"] = {"error": f"{type(e).__name__}: {e}"}
+        if comm is not None:
+            comm.close()
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -376,6 +388,43 @@ def run_b200(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def render_legs(plug, world, rank, local, comm, timed, ntab):
+    """spp*Mpix/s of BASELINE configs 2 (512^2, 64 spp, one sphere, one table) and 5 (1024^2, 256 spp,
+    10 x 10 spheres, `ntab` tables, all replicated) through merl_render; whole-job figure over all ranks."""
+    import torch
+    from mitsuba_customization_b200 import bsdf, render as RD, synth
+    dev = f"cuda:{local}"
+    out = {}
+
+    def leg(name, sc, w, h, spp, depth, reps):
+        rng = RD.spp_share(spp, world, rank)
+        film = torch.zeros(h, w, 4, device=dev)
+
+        def step():
+            film.zero_()
+            RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=rng, film=film)
+            if comm is not None:
+                comm.allreduce_sum_(film)
+        ms, _ = timed(step, reps, 2)
+        ms /= reps
+        out[name] = {"width": w, "height": h, "spp": spp, "max_depth": depth, "ms": ms,
+                     "spp_mpix_per_s": spp * w * h / 1e6 / (ms * 1e-3),
+                     "mean_radiance": [float(x) for x in film[..., :3].mean(dim=(0, 1))],
+                     "sample_share_min_max": [float(film[..., 3].min()), float(film[..., 3].max())]}
+        del film
+
+    leg("cfg2", RD.sphere_scene(plug), 512, 512, 64, 8, 5)
+    if ntab > 0:
+        t0 = time.time()
+        plugs = [bsdf.MERL(data=synth.synthetic_table(k), device=dev) for k in range(ntab)]
+        build_s = time.time() - t0
+        leg("cfg5", RD.grid_scene(plugs, 10, 10), 1024, 1024, 256, 8, 3)
+        out["cfg5"].update({"tables": ntab, "table_bytes_per_gpu": int(sum(p.info.table_bytes for p in plugs)),
+                            "table_build_s": build_s})
+        del plugs
+    return out
 
 
 def main():
