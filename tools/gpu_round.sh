@@ -11,7 +11,7 @@ if [ -x tools/microbench ]; then timeout 120 tools/microbench > gpurun_out/micro
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 timeout 300 python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
-  --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline \
+  --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-render \
   > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 3 -c 1 \
   -o gpurun_out/eval_pdf_full -f python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-extras \
