@@ -93,6 +93,28 @@ def _mask(active, n, device):
     return active.to(torch.uint8).contiguous()
 
 
+class _EvalOp(torch.autograd.Function):
+    """The table lookup as one autograd node (the torch twin of plugins/mitsuba3/merl_eval_op.h): forward =
+    merl_eval, backward = merl_backward into a zeroed (ncell, 4) gradient whose hit-count lane is cleared
+    (that lane of the table holds validity bits).  `cells` is the plugin's own table view; the kernel reads
+    it through the table handle, the argument only ties the node to the leaf."""
+
+    @staticmethod
+    def forward(fctx, cells, plug, ctx, si, wo, active):
+        fctx.plug, fctx.si, fctx.wo, fctx.active = plug, si, wo, active
+        fctx.enabled = plug._enabled(ctx)
+        return plug.eval(ctx, si, wo, active)
+
+    @staticmethod
+    def backward(fctx, grad_out):
+        plug = fctx.plug
+        grad = torch.zeros(plug.info.ncell, 4, dtype=torch.float32, device=grad_out.device)
+        if fctx.enabled:
+            plug.backward(fctx.si, fctx.wo, grad_out.contiguous(), active=fctx.active, grad_cells=grad)
+            check(_cabi.lib().merl_grad_clear_counts(plug._h, C.c_void_p(grad.data_ptr()), _stream(grad.device)))
+        return grad, None, None, None, None, None
+
+
 def _stream(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
@@ -235,6 +257,14 @@ class MERL:
                                     _ptr(wo[2]), _ptr(m), n, _ptr(out[0]), _ptr(out[1]), _ptr(out[2]),
                                     _stream(wi.device)))
         return out
+
+    def eval_ad(self, ctx, si, wo, cells, active=True):
+        """eval() differentiable with respect to the table: `cells` is `self.cells()` with requires_grad
+        set (the parameter `data` of traverse()); `loss.backward()` leaves d loss / d cells in `cells.grad`
+        ((ncell, 4), validity lane zero).  After an in-place optimiser step call parameters_changed()."""
+        if cells.data_ptr() != self.info.d_cells or tuple(cells.shape) != (self.info.ncell, 4):
+            raise MerlError("cells must be this plugin's own table view (self.cells())")
+        return _EvalOp.apply(cells, self, ctx, si, wo, active)
 
     def pdf(self, ctx, si, wo, active=True):
         wi, wo = _vec(si.wi, "si.wi"), _vec(wo, "wo")

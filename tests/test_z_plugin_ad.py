@@ -60,3 +60,38 @@ def test_mitsuba3_custom_op_matches_ctypes_backward(ad_binary, kind, tmp_path):
     assert np.all(np.abs(grad[:, :3] - ref[:, :3]) <= ATOL + RTOL * np.abs(ref[:, :3]))
     assert np.all(grad[:, 3] == 0) and direct[:, 3].sum() == ref[:, 3].sum()
     assert np.array_equal(after, 2 * rgb)
+
+
+def test_python_eval_ad_matches_backward(raw_table):
+    """The torch twin of the CustomOp: loss.backward() through MERL.eval_ad leaves in cells.grad what
+    MERL.backward computes, with the validity lane zero; one in-place SGD step + parameters_changed()
+    is followed exactly by eval (nearest-bin lookup: eval is linear in the cell)."""
+    from mitsuba_customization_b200 import bsdf, synth
+    plug = bsdf.MERL(data=raw_table, device="cuda:0")
+    n = 1 << 16
+    wi_h, wo_h = synth.random_queries(n, seed=53)
+    wi, wo = torch.from_numpy(wi_h).cuda(), torch.from_numpy(wo_h).cuda()
+    ctx, si = bsdf.BSDFContext(), bsdf.SurfaceInteraction3f(wi=wi)
+    gen = torch.Generator(device="cuda"); gen.manual_seed(5)
+    g = torch.rand(3, n, device="cuda", generator=gen)
+    cells = plug.cells().requires_grad_()
+    rgb = plug.eval_ad(ctx, si, wo, cells)
+    assert torch.equal(rgb.detach(), plug.eval(ctx, si, wo))
+    (rgb * g).sum().backward()
+    ref = plug.backward(si, wo, g)
+    assert cells.grad.shape == ref.shape
+    err = (cells.grad[:, :3].double() - ref[:, :3].double()).abs()
+    assert bool((err <= ATOL + RTOL * ref[:, :3].double().abs()).all())
+    assert bool((cells.grad[:, 3] == 0).all()) and float(ref[:, 3].sum()) > 0
+    # validity bits untouched by a step on the rgb lanes (upwards: g >= 0, so the cells stay non-negative);
+    # eval follows the cells exactly
+    before = plug.eval(ctx, si, wo).clone()
+    idx = plug.bins(si, wo).long()
+    with torch.no_grad():
+        cells += 0.5 * cells.grad
+    plug.parameters_changed(("data",))
+    after = plug.eval(ctx, si, wo)
+    valid = (plug.cells()[:, 3].int()[idx][None, :] >> torch.arange(3, device="cuda")[:, None]) & 1
+    want = (plug.cells()[idx, :3].T * wo[2]) * valid * (wi[2] > 0) * (wo[2] > 0)
+    assert torch.allclose(after, want.float(), rtol=1e-6, atol=1e-7)
+    assert not torch.equal(after, before)
