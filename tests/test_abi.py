@@ -80,3 +80,25 @@ def test_no_cpu_fallback():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 assert "oracle" not in open(os.path.join(dirpath, f)).read().replace("the oracle", "").replace(
                     "oracle:", "").replace("oracle's", "").replace("CPU oracle", ""), f
+
+
+def test_header_is_plain_c(tmp_path):
+    """The boundary is a C ABI: the header must compile as strict C99 (what a C / cgo / JNI stub includes),
+    and a C program must link against the library without a C++ runtime in its own link line."""
+    import shutil
+    import subprocess
+    gcc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else shutil.which("gcc")
+    src = tmp_path / "c99.c"
+    src.write_text('#include "merl_b200.h"\n'
+                   'int main(void) { merl_table_params_t p; merl_table_params_default(&p);\n'
+                   '  return (p.nh == 90 && merl_abi_version() > 0 && merl_last_error() != 0) ? 0 : 1; }\n')
+    inc = os.path.join(ROOT, "include")
+    r = subprocess.run([gcc, "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", inc, "-fsyntax-only", str(src)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    libdir = os.path.join(ROOT, "mitsuba_customization_b200")
+    exe = tmp_path / "c99"
+    r = subprocess.run([gcc, "-std=c99", "-I", inc, str(src), "-o", str(exe), "-L", libdir, "-lmerl_b200",
+                        f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert subprocess.run([str(exe)]).returncode == 0        # defaults and diagnostics work without a GPU
