@@ -3,6 +3,7 @@
 // Kernels:  repack_kernel, cdf_build_kernel, dens_kernel (table build, one-off; here)
 //                          stream_kernel<Op> with Op = QueryOp / SampleOp / BackwardOp /
 //                          EvalPdfAosOp / SampleAosOp (merl_kernels.cuh)
+#include <nvtx3/nvToolsExt.h>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <math.h>
@@ -38,8 +39,18 @@ using namespace merl;
 #endif
 
 // ------------------------------------------------------------------------------------------
-// errors, counters
+// errors, counters, profiler ranges
 // ------------------------------------------------------------------------------------------
+// One NVTX range per public call: named spans in an nsys / ncu timeline of the
+// host renderer.  NVTX 3 is header-only and a no-op unless a tool injects itself into the process.
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define MERL_RANGE(name) NvtxRange nvtx_range_(name)
+
 static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0};
 static std::atomic<int> g_search_mode{0};
@@ -480,11 +491,13 @@ static int build_table(const double* planar, const merl_table_params_t* pin, int
 
 extern "C" int merl_table_create_from_host(const double* planar_rgb, const merl_table_params_t* p, int device,
                                            merl_table_t** out) {
+    MERL_RANGE("merl_table_create_from_host");
     return build_table(planar_rgb, p, device, out);
 }
 
 extern "C" int merl_table_create_from_file(const char* path, const merl_table_params_t* pin, int device,
                                            merl_table_t** out) {
+    MERL_RANGE("merl_table_create_from_file");
     if (!path || !out) return fail(MERL_ERR_ARG, "NULL argument");
     FILE* f = fopen(path, "rb");
     if (!f) return fail(MERL_ERR_IO, "cannot open '%s'", path);
@@ -543,6 +556,7 @@ extern "C" int merl_table_set_cdf(merl_table_t* t, const float* cdf_host) {
 // it in place on the device.  This re-derives what depends on it -- the sampler's CDF rows and the
 // density table -- asynchronously on `stream` (Mitsuba 3: parameters_changed({"data"})).
 extern "C" int merl_table_refresh_sampler(merl_table_t* t, merl_stream_t stream) {
+    MERL_RANGE("merl_table_refresh_sampler");
     if (!t) return fail(MERL_ERR_ARG, "NULL argument");
     DeviceGuard g(t->device);
     return upload_sampler(t, nullptr, (cudaStream_t)stream);
@@ -551,6 +565,7 @@ extern "C" int merl_table_refresh_sampler(merl_table_t* t, merl_stream_t stream)
 // The optimiser's copy of the parameter -> the table the kernels read (Dr.Jit replaces parameter
 // arrays rather than writing into them), then what depends on it.
 extern "C" int merl_table_update_cells(merl_table_t* t, const void* cells4_device, merl_stream_t stream) {
+    MERL_RANGE("merl_table_update_cells");
     if (!t || !cells4_device) return fail(MERL_ERR_ARG, "NULL argument");
     DeviceGuard g(t->device);
     if (cells4_device != (const void*)t->d_cells)
@@ -657,6 +672,7 @@ extern "C" int merl_table_save_packed(const merl_table_t* t, const char* path) {
 }
 
 extern "C" int merl_table_create_from_packed(const char* path, int device, merl_table_t** out) {
+    MERL_RANGE("merl_table_create_from_packed");
     if (!path || !out) return fail(MERL_ERR_ARG, "NULL argument");
     FILE* f = fopen(path, "rb");
     if (!f) return fail(MERL_ERR_IO, "cannot open '%s'", path);
@@ -687,6 +703,7 @@ extern "C" int merl_table_create_from_packed(const char* path, int device, merl_
 extern "C" int merl_bins(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
                          const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
                          int32_t* idx_out, merl_stream_t stream) {
+    MERL_RANGE("merl_bins");
     int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
     if (rc) return rc;
     if (n > 0 && !idx_out) return fail(MERL_ERR_ARG, "idx_out is NULL");
@@ -699,6 +716,7 @@ extern "C" int merl_bins(const merl_table_t* t, const float* wix, const float* w
 extern "C" int merl_eval(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
                          const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
                          float* r, float* g, float* b, merl_stream_t stream) {
+    MERL_RANGE("merl_eval");
     int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
     if (rc) return rc;
     if (n > 0 && (!r || !g || !b)) return fail(MERL_ERR_ARG, "output pointer is NULL");
@@ -711,6 +729,7 @@ extern "C" int merl_eval(const merl_table_t* t, const float* wix, const float* w
 extern "C" int merl_pdf(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
                         const float* wox, const float* woy, const float* woz, const uint8_t* active, int64_t n,
                         float* pdf, merl_stream_t stream) {
+    MERL_RANGE("merl_pdf");
     int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
     if (rc) return rc;
     if (n > 0 && !pdf) return fail(MERL_ERR_ARG, "output pointer is NULL");
@@ -723,6 +742,7 @@ extern "C" int merl_pdf(const merl_table_t* t, const float* wix, const float* wi
 extern "C" int merl_eval_pdf(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
                              const float* wox, const float* woy, const float* woz, const uint8_t* active,
                              int64_t n, float* r, float* g, float* b, float* pdf, merl_stream_t stream) {
+    MERL_RANGE("merl_eval_pdf");
     int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
     if (rc) return rc;
     if (n > 0 && (!r || !g || !b || !pdf)) return fail(MERL_ERR_ARG, "output pointer is NULL");
@@ -763,6 +783,7 @@ extern "C" int merl_sample(const merl_table_t* t, const float* wix, const float*
                            const float* u1, const float* u2x, const float* u2y, const uint8_t* active, int64_t n,
                            float* wox, float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb,
                            uint32_t* lobe, merl_stream_t stream) {
+    MERL_RANGE("merl_sample");
     int rc = check_query_args(t, wix, wiy, wiz, u1, u2x, u2y, n);
     if (rc) return rc;
     if (n > 0 && (!wox || !woy || !woz || !pdf || !wr || !wg || !wb || !lobe))
@@ -812,6 +833,7 @@ extern "C" int merl_backward(const merl_table_t* t, const float* wix, const floa
                              const float* wox, const float* woy, const float* woz, const float* gr,
                              const float* gg, const float* gb, const uint8_t* active, int64_t n,
                              float* grad_cells4, uint32_t flags, merl_stream_t stream) {
+    MERL_RANGE("merl_backward");
     int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
     if (rc) return rc;
     if (n > 0 && (!gr || !gg || !gb || !grad_cells4)) return fail(MERL_ERR_ARG, "gradient pointer is NULL");
@@ -843,6 +865,7 @@ extern "C" int merl_grad_clear_counts(const merl_table_t* t, float* grad_cells4,
 
 extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const float* wo4, int64_t n, float* out4,
                                  merl_stream_t stream) {
+    MERL_RANGE("merl_eval_pdf_aos");
     if (!t || n < 0 || (n > 0 && (!wi4 || !wo4 || !out4))) return fail(MERL_ERR_ARG, "bad argument");
     if (!aligned(wi4, 16) || !aligned(wo4, 16) || !aligned(out4, 16))
         return fail(MERL_ERR_ARG, "AoS buffers must be 16-byte aligned");
@@ -854,6 +877,7 @@ extern "C" int merl_eval_pdf_aos(const merl_table_t* t, const float* wi4, const 
 
 extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const float* u4, int64_t n, float* wo4_out,
                                float* weight4_out, merl_stream_t stream) {
+    MERL_RANGE("merl_sample_aos");
     if (!t || n < 0 || (n > 0 && (!wi4 || !u4 || !wo4_out || !weight4_out))) return fail(MERL_ERR_ARG, "bad argument");
     if (!aligned(wi4, 16) || !aligned(u4, 16) || !aligned(wo4_out, 16) || !aligned(weight4_out, 16))
         return fail(MERL_ERR_ARG, "AoS buffers must be 16-byte aligned");
@@ -906,6 +930,7 @@ static void free_pipe(merl_table* t) {
 extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
                                   const float* wox, const float* woy, const float* woz, int64_t n, float* r,
                                   float* g, float* b, float* pdf) {
+    MERL_RANGE("merl_eval_pdf_host");
     int rc = check_query_args(tc, wix, wiy, wiz, wox, woy, woz, n);
     if (rc) return rc;
     if (n > 0 && (!r || !g || !b || !pdf)) return fail(MERL_ERR_ARG, "output pointer is NULL");
@@ -938,6 +963,7 @@ extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, cons
 extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
                                 const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
                                 float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe) {
+    MERL_RANGE("merl_sample_host");
     int rc = check_query_args(tc, wix, wiy, wiz, u1, u2x, u2y, n);
     if (rc) return rc;
     if (n > 0 && (!wox || !woy || !woz || !pdf || !wr || !wg || !wb || !lobe))
@@ -1048,6 +1074,7 @@ extern "C" int merl_comm_destroy(merl_comm_t* c) {
 }
 
 extern "C" int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_stream_t stream) {
+    MERL_RANGE("merl_allreduce_sum_f32");
     if (!c || count < 0 || (count > 0 && !buf)) return fail(MERL_ERR_ARG, "bad argument");
     if (count == 0) return MERL_OK;
     NcclApi* a = nccl_api();
@@ -1156,6 +1183,7 @@ extern "C" int merl_set_render_graphs(int on) {
 extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres, int nspheres,
                            const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out,
                            merl_stream_t stream_) {
+    MERL_RANGE("merl_render");
     if (!tables || !spheres || !p || !film4) return fail(MERL_ERR_ARG, "NULL argument");
     if (ntables < 1 || ntables > 1024) return fail(MERL_ERR_ARG, "ntables must be in [1, 1024]");
     if (nspheres < 1 || nspheres > kMaxSpheres) return fail(MERL_ERR_ARG, "nspheres must be in [1, %d]", kMaxSpheres);
