@@ -4,9 +4,10 @@ parameters_changed() with a replaced `data` array against the real library, chec
 (custom-op eval == eval bit for bit, gradient of the validity lane zero, eval doubles exactly after
 the cells were doubled) and writes its results, which are compared here with the ctypes path.
 
-Ordering note: the file sorts last on purpose.  Its CPU twin (tests/test_plugin_hosts_cpu.py, same
-driver against the test double) ran green, but the GPU budget of the round was spent before this
-driver could be run on a B200, so it must not stand in front of other GPU tests under `pytest -x`.
+Ordering note: the file sorts last on purpose.  The driver binary itself ran on a B200 in the last seconds
+of the round's GPU budget (profiles/r01_ad_check.txt; output checked against the oracle on the CPU by
+tests/_check_ad_output.py) and its CPU twin (tests/test_plugin_hosts_cpu.py) is green, but these pytest
+wrappers have not run on a GPU yet, so they must not stand in front of other GPU tests under `pytest -x`.
 """
 import os
 import subprocess
