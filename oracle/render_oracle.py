@@ -46,6 +46,9 @@ def render(tables, spheres, *, width, height, spp, max_depth, seed, cam_pos, cam
            fov_x_deg=40.0, env=(1.0, 1.0, 1.0), spp_begin=0, spp_end=None):
     """tables: list of OracleTable (CDF installed); spheres: [(cx, cy, cz, radius, material)].
     Returns the film, (height, width, 4) float64: rgb and the sample-count share."""
+    for k, t in enumerate(tables):
+        if not t.t.cdf or not t.t.dens:
+            raise ValueError(f"table {k} has no sampler CDF installed (build_cdf() / set_cdf() first)")
     arr = (O._Table * len(tables))(*[t.t for t in tables])
     sph = np.ascontiguousarray([[s[0], s[1], s[2], s[3]] for s in spheres], dtype=np.float64)
     mat = np.ascontiguousarray([int(s[4]) for s in spheres], dtype=np.int32)

@@ -81,3 +81,34 @@ def test_two_rank_gloo_sharded_backward(tmp_path):
     world, port = 2, _free_port()
     mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
     assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+
+
+def _render_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # every rank renders its share of the sample indices of every pixel (render.spp_share, the split
+        # merl_render's spp_begin / spp_end express); one allreduce of the film gives the full image
+        from mitsuba_customization_b200 import render as RD, synth
+        from oracle import merl_oracle as O, render_oracle as R
+        t = O.OracleTable(synth.synthetic_table(0))
+        t.build_cdf()
+        kw = dict(width=20, height=16, spp=5, max_depth=3, seed=11, cam_pos=(0.0, -4.0, 0.0), cam_target=(0.0, 0.0, 0.0),
+                  fov_x_deg=40.0)
+        lo, hi = RD.spp_share(kw["spp"], world, rank)
+        film = torch.from_numpy(R.render([t], [(0, 0, 0, 1.0, 0)], spp_begin=lo, spp_end=hi, **kw).copy())
+        dist.all_reduce(film)
+        if rank == 0:
+            full = R.render([t], [(0, 0, 0, 1.0, 0)], **kw)
+            np.testing.assert_allclose(film.numpy(), full, rtol=1e-12, atol=1e-15)
+            np.testing.assert_allclose(film.numpy()[..., 3], 1.0, atol=1e-12)      # every sample rendered exactly once
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_sample_sharded_render_sums_to_the_full_film(tmp_path, world):
+    port = _free_port()
+    mp.spawn(_render_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))

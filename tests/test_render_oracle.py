@@ -35,3 +35,9 @@ def test_sample_ranges_add_up(oracle_table):
     a = R.render([oracle_table], [(0, 0, 0, 1.0, 0)], spp_begin=0, spp_end=2, **kw)
     b = R.render([oracle_table], [(0, 0, 0, 1.0, 0)], spp_begin=2, spp_end=6, **kw)
     np.testing.assert_allclose(a + b, full, rtol=1e-12, atol=1e-15)
+
+
+def test_render_refuses_a_table_without_sampler(raw_table):
+    from oracle import merl_oracle as O
+    with pytest.raises(ValueError):
+        R.render([O.OracleTable(raw_table)], [(0, 0, 0, 1.0, 0)], width=4, height=4, spp=1, max_depth=1, seed=1, **CAM)
