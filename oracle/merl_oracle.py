@@ -120,6 +120,9 @@ class OracleTable:
         return out
 
     def eval_pdf(self, wi, wo, want_pdf=True):
+        if want_pdf and self.cdf is None:
+            # the C side would return the cosine lobe's share only: a silently incomplete density
+            raise ValueError("pdf needs the sampler CDF (set_cdf / build_cdf); pass want_pdf=False for eval alone")
         wi, wo = _dirs(wi), _dirs(wo)
         n = wi.shape[1]
         rgb = np.empty((3, n), dtype=np.float64)
