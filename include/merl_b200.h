@@ -12,7 +12,8 @@
  *               wo in the local frame, Mask active)            -> merl_eval* / merl_pdf / merl_sample
  *   Mitsuba 0.6 BSDF::eval / pdf / sample (BSDFSamplingRecord)  -> the *_aos entry points
  *   plugin ctor reading `filename` (MERL .binary)              -> merl_table_create_from_file
- *   Dr.Jit AD of the table gather (scatter_reduce)             -> merl_backward
+ *   Dr.Jit AD of the table gather (scatter_reduce)             -> merl_backward (+ merl_grad_clear_counts)
+ *   parameters_changed({"data"}) after an optimiser step       -> merl_table_refresh_sampler / _update_cells
  *
  * Conventions
  *   - Every query/result pointer is a DEVICE pointer owned by the caller (a Dr.Jit
@@ -22,8 +23,10 @@
  *   - SoA: a Vector3f is three float arrays x[n], y[n], z[n] (Dr.Jit layout).
  *     AoS: float4 per query (xyz + pad) for the 0.6 wavefront stage.
  *   - All launches are asynchronous on `stream` (a cudaStream_t; NULL = default stream);
- *     no hidden device synchronisation.  Table handles are immutable after creation and
- *     may be used from any thread.
+ *     no hidden device synchronisation.  A table handle may be used from any thread; it
+ *     changes only through merl_table_set_cdf / _refresh_sampler / _update_cells (or the
+ *     caller writing d_cells), which are ordered on their stream like any launch and must
+ *     not overlap queries on other streams.
  *   - Return 0 on success, a negative merl_status otherwise; merl_last_error() returns a
  *     thread-local message.  No exception crosses this boundary.  There is no CPU
  *     fallback: without a CUDA device every compute entry point fails with MERL_ERR_CUDA.
