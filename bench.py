@@ -7,13 +7,21 @@ A "step" is one pass of the hot path (batched eval+pdf through the plugin's eval
 through the C ABI) over one batch of 2^26 synthetic (wi, wo) pairs per GPU against one
 synthetic MERL table.  One JSON line is printed by rank 0:
 
-  value      whole-job Gquery/s with the batch resident in HBM (CUDA events, max over ranks)
+  value      whole-job Gquery/s with the batch resident in HBM (CUDA events, max over ranks), timed
+             over exactly K steps that follow W + `--preheat` untimed steps, i.e. in the SUSTAINED
+             state a renderer holds the kernel in (the first ~30 ms after an idle period run 7-14 %
+             faster: that burst figure is extras.eval_pdf_burst)
   e2e        the same metric through merl_eval_pdf_host with PINNED HOST buffers: every step
              copies the 24 B/query of inputs host->device and the 16 B/query of results back
   roofline   achieved algorithmic HBM GB/s (40 B/query) of the eval_pdf kernel
              against the measured copy bandwidth in MEASURED_PEAKS.json
   cpu_baseline  the CPU oracle (kind "port": the reference has no source to run) on a bounded
-             sample of the same workload, all host threads
+             sample of the same workload, all host threads, plus BASELINE config 1 (2^20 pairs,
+             eval+pdf+sample, single thread and all threads); run in a SUBPROCESS so that the GPU
+             arm's process never loads anything under oracle/
+  extras.grad_scaling   the sharded gradient pass (backward + exchange): peer-memory kernel vs NCCL,
+             one exchange per 1 / 4 / 16 batches, BASELINE config 4, and an on-box correctness check
+  extras.render         BASELINE configs 2 and 5 (spp*Mpix/s), and config 5 sharded by table
 
 --impl reference times that CPU port alone (the reference's own plugins cannot be built:
 /root/reference holds no source).
@@ -23,6 +31,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -43,12 +52,15 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--preheat", type=int, default=150,
+                    help="extra untimed steps right before the timed ones (sustained state); 0 = burst figure")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log2-batch", type=int, default=LOG2_BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--no-render", action="store_true", help="skip the render legs of the extras")
     ap.add_argument("--render-tables", type=int, default=100, help="tables of render config 5 (0 = skip it)")
+    ap.add_argument("--cpu-legs", action="store_true", help="(internal) print the CPU legs as JSON and exit")
     return ap.parse_args()
 
 
@@ -69,27 +81,71 @@ def recorded_traffic():
 
 
 # --------------------------------------------------------------------------------------------
-# CPU arm: the oracle port, all host threads, bounded sample
+# CPU arm: the oracle port on the box's host cores (bounded samples)
 # --------------------------------------------------------------------------------------------
-def cpu_port_rate(budget_s=10.0, log2_sample=22):
+def host_threads():
+    """Threads this process may use: the affinity mask, NOT OMP_NUM_THREADS (torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which made the round-1 reference arm single-threaded at N > 1)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def _rate(fn, n, budget_s, max_reps=256):
+    fn()
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        fn()
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or reps >= max_reps:
+            return n * reps / dt / 1e9, reps, dt
+
+
+def cpu_legs(budget_s=8.0):
+    """All CPU figures of the line.  Runs in its own process (bench.py --cpu-legs)."""
     import numpy as np
     from mitsuba_customization_b200 import synth
     from oracle import merl_oracle as O
 
+    cores = host_threads()
     raw = synth.synthetic_table(0)
     t = O.OracleTable(raw)
     t.build_cdf()
-    n = 1 << log2_sample
+    out = {"cores": cores}
+    # headline sample: 2^22 of the step's 2^26 queries, all threads
+    n = 1 << 22
     wi, wo = synth.random_queries(n, seed=1234)
-    t.eval_pdf(wi[:, :4096], wo[:, :4096])  # thread pool warm-up
-    reps, t0 = 0, time.perf_counter()
-    while True:
-        t.eval_pdf(wi, wo)
-        reps += 1
-        dt = time.perf_counter() - t0
-        if dt >= budget_s or reps >= 256:
-            break
-    return n * reps / dt / 1e9, O.max_threads(), f"{reps} x 2^{log2_sample} eval+pdf queries of the same workload, {dt:.1f} s"
+    O.set_threads(cores)
+    v, reps, dt = _rate(lambda: t.eval_pdf(wi, wo), n, budget_s)
+    out["eval_pdf_all_threads"] = {"gquery_s": v, "sample": f"{reps} x 2^22 eval+pdf queries of the same workload, {dt:.1f} s"}
+    # BASELINE config 1: 2^20 pairs, eval + pdf + sample, single thread and all threads
+    m = 1 << 20
+    rng = np.random.default_rng(3)
+    u1 = rng.random(m, dtype=np.float32)
+    u2 = rng.random((2, m), dtype=np.float32)
+    a, b = wi[:, :m].copy(), wo[:, :m].copy()
+    cfg1 = {"pairs": m}
+    for name, nt in (("single_thread", 1), ("all_threads", cores)):
+        O.set_threads(nt)
+        ve, _, _ = _rate(lambda: t.eval_pdf(a, b), m, 2.0, 64)
+        vs, _, _ = _rate(lambda: t.sample(a, u1, u2), m, 2.0, 64)
+        cfg1[name] = {"threads": nt, "eval_pdf_gquery_s": ve, "sample_gquery_s": vs,
+                      "eval_pdf_sample_ms": m / ve / 1e6 + m / vs / 1e6}
+    out["config1_2p20"] = cfg1
+    return out
+
+
+def cpu_legs_subprocess():
+    env = dict(os.environ)
+    for k in ("OMP_NUM_THREADS", "RANK", "LOCAL_RANK", "WORLD_SIZE"):
+        env.pop(k, None)
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-legs"], capture_output=True, text=True, env=env,
+                       cwd=ROOT, timeout=600)
+    if r.returncode != 0:
+        raise RuntimeError("cpu legs failed: " + r.stderr[-400:])
+    return json.loads(r.stdout.strip().splitlines()[-1])
 
 
 def run_reference(args):
@@ -100,6 +156,8 @@ def run_reference(args):
     from mitsuba_customization_b200 import synth
     from oracle import merl_oracle as O
 
+    cores = host_threads()
+    O.set_threads(cores)
     raw = synth.synthetic_table(0)
     t = O.OracleTable(raw)
     t.build_cdf()
@@ -119,10 +177,11 @@ def run_reference(args):
         "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "step_sample": "2^22 of the step's 2^26 queries per step (bounded CPU sample)"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": O.max_threads(), "kind": "port",
-                         "sample": f"{steps} steps x 2^22 eval+pdf queries, OpenMP over all host threads; the "
-                                   "reference's own plugins are absent from /root/reference, so this is the CPU "
-                                   "restatement (oracle/merl_oracle.c), not the reference binary"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{steps} steps x 2^22 eval+pdf queries, OpenMP over all {cores} host threads of the "
+                                   "affinity mask (OMP_NUM_THREADS ignored); the reference's own plugins are absent from "
+                                   "/root/reference, so this is the CPU restatement (oracle/merl_oracle.c), not the "
+                                   "reference binary"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -177,7 +236,7 @@ class ClockSampler(threading.Thread):
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "NVML unavailable"}
         s = sorted(self.samples)
         out = {"sm_mhz": s[len(s) // 2], "sm_min_mhz": s[0], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-               "samples": len(s), "window": "the timed region of the headline metric only"}
+               "samples": len(s), "window": "the preheat + timed region of the headline metric"}
         if self.power_w:
             out["power_w_max"] = max(self.power_w)
         return out
@@ -246,13 +305,13 @@ def run_b200(args):
             ms = float(t.item())
         return ms, launches
 
-    # ---- headline: device-resident eval+pdf ----------------------------------------------
+    # ---- headline: device-resident eval+pdf, sustained ------------------------------------------
     W = max(args.warmup, 3)
     for _ in range(W):                      # warm up before the clock sampler's window opens
         plug.eval_pdf(ctx, si, wo, out=out)
     torch.cuda.synchronize()
     sampler.start()
-    ms, launches = timed(lambda: plug.eval_pdf(ctx, si, wo, out=out), args.steps, 0)
+    ms, launches = timed(lambda: plug.eval_pdf(ctx, si, wo, out=out), args.steps, max(0, args.preheat))
     sampler.stop_flag = True
     sampler.join(timeout=1.0)
     ms_step = ms / args.steps
@@ -278,13 +337,19 @@ def run_b200(args):
         e2e_s = float(t.item())
     e2e_value = world * n * e2e_steps / e2e_s / 1e9
     checksum = float(hout[3, :: max(1, n // 4096)].double().sum())
+    del hwi, hwo, hout
 
     # ---- other kernels of the path (reported, not the headline) --------------------------
     extras = {}
+    peak, peak_src = measured_peak()
     if not args.no_extras:
-        # per-step times of the headline kernel over 200 back-to-back steps (one event pair per
-        # step): the first ~50 steps (~30 ms) run at the burst rate, after which the board's power
-        # management stretches each step by 7-14 %
+        # burst: what a caller sees for the first ~20 launches after an idle period
+        torch.cuda.synchronize()
+        time.sleep(0.5)
+        ms_b, _ = timed(lambda: plug.eval_pdf(ctx, si, wo, out=out), 20, 0)
+        extras["eval_pdf_burst"] = {"gquery_s_per_gpu": n / (ms_b / 20 * 1e-3) / 1e9, "steps": 20, "after_idle_s": 0.5,
+                                    "frac_of_hbm": BYTES_PER_QUERY * n / (ms_b / 20 * 1e-3) / 1e9 / peak}
+        # per-step times over 200 back-to-back steps after the same idle period (one event pair per step)
         torch.cuda.synchronize()
         time.sleep(0.5)
         ks = 200
@@ -302,6 +367,18 @@ def run_b200(args):
         ms_s, _ = timed(lambda: plug.sample(ctx, si, u1, u2), k, 3)
         extras["sample_gquery_s"] = world * n / (ms_s / k * 1e-3) / 1e9
         extras["sample_hbm_gbs_per_gpu"] = 56 * n / (ms_s / k * 1e-3) / 1e9
+        extras["sample_frac_of_hbm"] = extras["sample_hbm_gbs_per_gpu"] / peak
+        # BASELINE config 1 on the GPU: 2^20 pairs, eval+pdf then sample (launch-latency dominated: 42 MB is
+        # ~6 us at the roofline; reported, not used for any roofline fraction)
+        m20 = 1 << 20
+        s20 = bsdf.SurfaceInteraction3f(wi=wi[:, :m20].contiguous())
+        wo20, u120, u220, out20 = wo[:, :m20].contiguous(), u1[:m20].contiguous(), u2[:, :m20].contiguous(), torch.empty(4, m20, device=dev)
+        ms_e20, _ = timed(lambda: plug.eval_pdf(ctx, s20, wo20, out=out20), 50, 5)
+        ms_s20, _ = timed(lambda: plug.sample(ctx, s20, u120, u220), 50, 5)
+        extras["config1_2p20_gpu"] = {"pairs": m20, "eval_pdf_us": ms_e20 / 50 * 1e3, "sample_us": ms_s20 / 50 * 1e3,
+                                      "eval_pdf_gquery_s": m20 / (ms_e20 / 50 * 1e-3) / 1e9,
+                                      "sample_gquery_s": m20 / (ms_s20 / 50 * 1e-3) / 1e9}
+        del s20, wo20, u120, u220, out20
         # BASELINE config 3: customized_measurment plugin, 2^24-query eval / sample sweep, L2-resident table
         cdims = (64, 96, 192)
         cplug = bsdf.CustomizedMeasurement(data=synth.synthetic_table(7, dims=cdims, theta_h_sqrt=False), resolution=cdims,
@@ -315,42 +392,20 @@ def run_b200(args):
         extras["customized_2p24"] = {"resolution": list(cdims), "theta_h_mapping": "linear", "queries_per_gpu": m,
                                      "table_bytes": int(cplug.info.table_bytes),
                                      "eval_pdf_gquery_s": world * m / (ms_ce / k * 1e-3) / 1e9,
+                                     "eval_pdf_frac_of_hbm": BYTES_PER_QUERY * m / (ms_ce / k * 1e-3) / 1e9 / peak,
                                      "sample_gquery_s": world * m / (ms_cs / k * 1e-3) / 1e9}
         del cplug, csi, cwo, cu1, cu2, cout
         del u1, u2
-        g = torch.randn(3, n, device=dev, generator=gen)
-        grad = torch.zeros(plug.info.ncell, 4, device=dev)
-        ms_b, _ = timed(lambda: plug.backward(si, wo, g, grad_cells=grad), k, 3)
-        extras["backward_gquery_s_no_allreduce"] = world * n / (ms_b / k * 1e-3) / 1e9
         comm = None
         if world > 1:
             from mitsuba_customization_b200 import distributed as D
             comm = D.Comm(rank, world, local)   # libmerl_b200's NCCL communicator (id shipped over torch.distributed)
-
-            def bwd_ar():
-                plug.backward(si, wo, g, grad_cells=grad)
-                comm.allreduce_sum_(grad)
-            ms_ba, _ = timed(bwd_ar, k, 3)
-            extras["backward_gquery_s_with_allreduce"] = world * n / (ms_ba / k * 1e-3) / 1e9
-            ms_ar, _ = timed(lambda: comm.allreduce_sum_(grad), k, 3)
-            extras["allreduce_ms"] = ms_ar / k
-            extras["allreduce_bytes"] = grad.numel() * 4
-            # BASELINE config 4: 2^26 queries in TOTAL, sharded over the ranks (strong scaling), one allreduce
-            lo, hi = D.shard_bounds(1 << 26, world, rank)
-            m = min(hi - lo, n)
-            sw = bsdf.SurfaceInteraction3f(wi=wi[:, :m].contiguous())
-            swo, sg = wo[:, :m].contiguous(), g[:, :m].contiguous()
-
-            def bwd_strong():
-                plug.backward(sw, swo, sg, grad_cells=grad)
-                comm.allreduce_sum_(grad)
-            ms_bs, _ = timed(bwd_strong, k, 3)
-            extras["backward_2p26_total_ms_with_allreduce"] = ms_bs / k
-            extras["backward_2p26_total_gquery_s"] = (1 << 26) / (ms_bs / k * 1e-3) / 1e9
-            del sw, swo, sg
-        del g, grad
+        try:
+            extras["grad_scaling"] = grad_legs(plug, si, wo, n, world, rank, local, comm, timed, gen, k)
+        except Exception as e:  # noqa: BLE001
+            extras["grad_scaling"] = {"error": f"{type(e).__name__}: {e}"}
         # BASELINE configs 2 and 5 (the metric's spp*Mpix/s @ 1/2/4/8): the wavefront harness around the
-        # BSDF stage; every rank renders its share of the sample indices, films summed with one allreduce.
+        # BSDF stage; every rank renders its share of the sample indices, films summed with one exchange.
         # A failure here is reported in the line, it never takes the headline down.
         if not args.no_render:
             try:
@@ -361,10 +416,21 @@ def run_b200(args):
             comm.close()
 
     if rank == 0:
-        peak, peak_src = measured_peak()
         achieved = BYTES_PER_QUERY * n / (kernel_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": recorded_traffic(), "peak_source": peak_src,
+                "algorithmic_bytes_per_query": BYTES_PER_QUERY, "kernel": "stream_kernel<QueryOp<EVAL_PDF,4>,3>",
+                "kernel_ms": kernel_ms,
+                "state": f"sustained: timed after {W} + {max(0, args.preheat)} untimed steps" if args.preheat > 0 else "burst"}
+        if args.preheat > 0:
+            roof["frac_sustained"] = achieved / peak
+        if "eval_pdf_burst" in extras:
+            roof["frac_burst"] = extras["eval_pdf_burst"]["frac_of_hbm"]
+        if "customized_2p24" in extras:
+            roof["frac_config3_customized_2p24"] = extras["customized_2p24"]["eval_pdf_frac_of_hbm"]
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": W + max(0, args.preheat),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "queries_per_gpu_per_step": n, "table": "synthetic MERL id 0",
@@ -376,60 +442,217 @@ def run_b200(args):
                     "steps": e2e_steps, "call": "MERL.eval_pdf_host -> merl_eval_pdf_host (pinned host buffers)",
                     "result_checksum": checksum},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": recorded_traffic(), "peak_source": peak_src,
-                         "algorithmic_bytes_per_query": BYTES_PER_QUERY, "kernel": "stream_kernel<QueryOp<EVAL_PDF,4>,3>",
-                         "kernel_ms": kernel_ms},
+            "roofline": roof,
             "extras": extras,
         }
         if world == 1 and not args.no_cpu_baseline:
-            v, cores, sample = cpu_port_rate()
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+            try:
+                c = cpu_legs_subprocess()
+                line["cpu_baseline"] = {"value": c["eval_pdf_all_threads"]["gquery_s"], "unit": UNIT, "cores": c["cores"],
+                                        "kind": "port", "sample": c["eval_pdf_all_threads"]["sample"],
+                                        "single_thread": c["config1_2p20"]["single_thread"]["eval_pdf_gquery_s"],
+                                        "sample_gquery_s": c["config1_2p20"]["all_threads"]["sample_gquery_s"],
+                                        "config1_2p20": c["config1_2p20"],
+                                        "process": "subprocess (bench.py --cpu-legs): the GPU arm never loads oracle/"}
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+def grad_legs(plug, si, wo, n, world, rank, local, comm, timed, gen, k):
+    """The sharded gradient pass (BASELINE config 4; north_star's scaling target): scatter-add of this rank's
+    query shard into its private gradient table + ONE exchange that sums the tables over the ranks."""
+    import torch
+    import torch.distributed as dist
+    from mitsuba_customization_b200 import bsdf
+    from mitsuba_customization_b200 import distributed as D
+    dev = torch.device("cuda", local)
+    ncell = plug.info.ncell
+    g = torch.randn(3, n, device=dev, generator=gen)
+    out = {"queries_per_gpu_per_batch": n, "exchange_bytes": ncell * 16}
+    grad_plain = torch.zeros(ncell, 4, device=dev)
+    ms_b, _ = timed(lambda: plug.backward(si, wo, g, grad_cells=grad_plain), k, 3)
+    out["backward_gquery_s_no_exchange"] = world * n / (ms_b / k * 1e-3) / 1e9
+    out["backward_gquery_s_per_gpu_no_exchange"] = n / (ms_b / k * 1e-3) / 1e9
+    out["backward_frac_of_hbm"] = 36 * n / (ms_b / k * 1e-3) / 1e9 / measured_peak()[0]
+    if comm is None:
+        # one GPU: the deferred-mask form the multi-GPU path uses (mask applied once per exchange)
+        ms_d, _ = timed(lambda: (plug.backward(si, wo, g, grad_cells=grad_plain, defer_mask=True),
+                                 plug.apply_grad_mask(grad_plain)), k, 3)
+        out["backward_gquery_s_deferred_mask"] = n / (ms_d / k * 1e-3) / 1e9
+        return out
+
+    transports = {}
+    bufs = {"peer": D.PeerBuffer(comm, 4 * ncell, "peer"), "nccl_registered": D.PeerBuffer(comm, 4 * ncell, "nccl")}
+    for name, pb in bufs.items():
+        gt = pb.tensor((ncell, 4))
+        res = {"registration": pb.registration}
+        ms_x, _ = timed(lambda: pb.allreduce_(mask_plug=plug), k, 3)
+        res["exchange_ms"] = ms_x / k
+        res["exchange_bus_gbs"] = 2 * (world - 1) / world * ncell * 16 / (ms_x / k * 1e-3) / 1e9
+        for m in (1, 4, 16):
+            def step():
+                for _ in range(m):
+                    plug.backward(si, wo, g, grad_cells=gt, defer_mask=True)
+                pb.allreduce_(mask_plug=plug)
+            reps = max(2, k // m)
+            ms_w, _ = timed(step, reps, 2)
+            v = world * n * m / (ms_w / reps * 1e-3) / 1e9
+            res[f"weak_gquery_s_exchange_every_{m}"] = v
+            res[f"weak_efficiency_vs_no_exchange_every_{m}"] = v / out["backward_gquery_s_no_exchange"]
+        transports[name] = res
+    # round 1's form, for comparison: ncclAllReduce on an unregistered torch tensor + separate mask pass
+    def plain():
+        plug.backward(si, wo, g, grad_cells=grad_plain)
+        comm.allreduce_sum_(grad_plain)
+    ms_p, _ = timed(plain, k, 3)
+    ms_px, _ = timed(lambda: comm.allreduce_sum_(grad_plain), k, 3)
+    transports["nccl_unregistered"] = {"exchange_ms": ms_px / k,
+                                       "exchange_bus_gbs": 2 * (world - 1) / world * ncell * 16 / (ms_px / k * 1e-3) / 1e9,
+                                       "weak_gquery_s_exchange_every_1": world * n / (ms_p / k * 1e-3) / 1e9,
+                                       "weak_efficiency_vs_no_exchange_every_1":
+                                           world * n / (ms_p / k * 1e-3) / 1e9 / out["backward_gquery_s_no_exchange"]}
+    out["transports"] = transports
+
+    # BASELINE config 4: 2^26 queries in TOTAL, sharded over the ranks (strong scaling), one exchange
+    lo, hi = D.shard_bounds(1 << 26, world, rank)
+    m4 = min(hi - lo, n)
+    sw = bsdf.SurfaceInteraction3f(wi=si.wi[:, :m4].contiguous())
+    swo, sg = wo[:, :m4].contiguous(), g[:, :m4].contiguous()
+    cfg4 = {"total_queries": 1 << 26, "queries_per_gpu": m4}
+    for name, pb in bufs.items():
+        gt = pb.tensor((ncell, 4))
+
+        def strong():
+            plug.backward(sw, swo, sg, grad_cells=gt, defer_mask=True)
+            pb.allreduce_(mask_plug=plug)
+        ms_s, _ = timed(strong, k, 3)
+        cfg4[f"{name}_ms"] = ms_s / k
+        cfg4[f"{name}_gquery_s"] = (1 << 26) / (ms_s / k * 1e-3) / 1e9
+    ms_c, _ = timed(lambda: plug.backward(sw, swo, sg, grad_cells=grad_plain, defer_mask=True), k, 3)
+    cfg4["scatter_only_ms"] = ms_c / k
+    out["config4_2p26_total"] = cfg4
+
+    # correctness of the exchange on this box: every rank scatters ITS shard of 2^22 x world seeded queries
+    # and exchanges; rank-local recomputation of ALL shards must agree, hit counts must sum exactly
+    mq = 1 << 22
+    checks = {}
+    full = torch.zeros(ncell, 4, device=dev)
+    shards = []
+    for r in range(world):
+        gg = torch.Generator(device=dev)
+        gg.manual_seed(777 + r)
+        a, b = hemisphere(mq, gg, dev), hemisphere(mq, gg, dev)
+        c = torch.randn(3, mq, device=dev, generator=gg)
+        plug.backward(bsdf.SurfaceInteraction3f(wi=a), b, c, grad_cells=full)
+        if r == rank:
+            shards = [a, b, c]
+    for name, pb in bufs.items():
+        gt = pb.tensor((ncell, 4))
+        gt.zero_()
+        plug.backward(bsdf.SurfaceInteraction3f(wi=shards[0]), shards[1], shards[2], grad_cells=gt, defer_mask=True)
+        pb.allreduce_(mask_plug=plug)
+        torch.cuda.synchronize()
+        hits = float(gt[:, 3].double().sum())
+        scale = float(full[:, :3].abs().max())
+        err = float((gt[:, :3] - full[:, :3]).abs().max()) / max(scale, 1e-30)
+        sums = torch.tensor([float(gt.double().sum())], device=dev, dtype=torch.float64)
+        allsums = [torch.zeros_like(sums) for _ in range(world)]
+        dist.all_gather(allsums, sums)
+        same = all(float(x) == float(allsums[0]) for x in allsums)
+        ok = hits == float(world * mq) and err <= 2e-5 and pb.status() == 0 and (same or name != "peer")
+        checks[name] = {"ok": bool(ok), "hit_count_sum": hits, "expected_hits": world * mq, "max_err_over_max": err,
+                        "bitwise_same_on_all_ranks": bool(same)}
+    flag = torch.tensor([1.0 if all(c["ok"] for c in checks.values()) else 0.0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    out["allreduce_check"] = "ok" if float(flag) == 1.0 else "FAILED"
+    out["allreduce_check_detail"] = checks
+    for pb in bufs.values():
+        pb.close()
+    if out["allreduce_check"] != "ok":
+        raise RuntimeError(f"gradient exchange check failed: {checks}")
+    return out
+
+
 def render_legs(plug, world, rank, local, comm, timed, ntab):
     """spp*Mpix/s of BASELINE configs 2 (512^2, 64 spp, one sphere, one table) and 5 (1024^2, 256 spp,
-    10 x 10 spheres, `ntab` tables, all replicated) through merl_render; whole-job figure over all ranks."""
+    10 x 10 spheres, `ntab` tables, all replicated) through merl_render; whole-job figure over all ranks.
+    Multi-GPU: films live in an exchange buffer and are summed by the peer-memory kernel."""
     import torch
     from mitsuba_customization_b200 import bsdf, render as RD, synth
+    from mitsuba_customization_b200 import distributed as D
     dev = f"cuda:{local}"
     out = {}
 
     def leg(name, sc, w, h, spp, depth, reps):
         rng = RD.spp_share(spp, world, rank)
-        film = torch.zeros(h, w, 4, device=dev)
+        pb = D.PeerBuffer(comm, w * h * 4, "peer") if comm is not None else None
+        film = pb.tensor((h, w, 4)) if pb is not None else torch.zeros(h, w, 4, device=dev)
 
         def step():
             film.zero_()
             RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=rng, film=film)
-            if comm is not None:
-                comm.allreduce_sum_(film)
+            if pb is not None:
+                pb.allreduce_()
         ms, _ = timed(step, reps, 2)
         ms /= reps
         out[name] = {"width": w, "height": h, "spp": spp, "max_depth": depth, "ms": ms,
                      "spp_mpix_per_s": spp * w * h / 1e6 / (ms * 1e-3),
                      "mean_radiance": [float(x) for x in film[..., :3].mean(dim=(0, 1))],
-                     "sample_share_min_max": [float(film[..., 3].min()), float(film[..., 3].max())]}
+                     "sample_share_min_max": [float(film[..., 3].min()), float(film[..., 3].max())],
+                     "film_exchange": "peer-memory kernel" if pb is not None else "none (1 GPU)"}
         del film
+        if pb is not None:
+            pb.close()
 
     leg("cfg2", RD.sphere_scene(plug), 512, 512, 64, 8, 5)
     if ntab > 0:
         t0 = time.time()
         plugs = [bsdf.MERL(data=synth.synthetic_table(k), device=dev) for k in range(ntab)]
         build_s = time.time() - t0
-        leg("cfg5", RD.grid_scene(plugs, 10, 10), 1024, 1024, 256, 8, 3)
+        sc5 = RD.grid_scene(plugs, 10, 10)
+        leg("cfg5", sc5, 1024, 1024, 256, 8, 3)
         out["cfg5"].update({"tables": ntab, "table_bytes_per_gpu": int(sum(p.info.table_bytes for p in plugs)),
-                            "table_build_s": build_s})
+                            "table_build_s": build_s, "sharding": "samples (tables replicated)"})
+        if comm is not None:
+            # the by-table variant (BASELINE config 5 "sharded by table"): every rank traces everything, evaluates
+            # only its own tables, one exchange of the stage outputs per bounce.  Fewer samples: it is ~world x slower.
+            wave = 1 << 21
+            xb = D.PeerBuffer(comm, 12 * wave, "peer")
+            own = [p if kk % world == rank else None for kk, p in enumerate(plugs)]
+            scb = RD.grid_scene(own, 10, 10)
+            film_b = torch.zeros(1024, 1024, 4, device=dev)
+            film_r = torch.zeros(1024, 1024, 4, device=dev)
+            spp_b = 16
+
+            def step_b():
+                film_b.zero_()
+                RD.render(scb, 1024, 1024, spp_b, max_depth=8, seed=1, film=film_b, wavefront=wave,
+                          table_shard=(world, rank), stage_exchange=xb)
+            ms_b, _ = timed(step_b, 2, 1)
+            ms_b /= 2
+            RD.render(sc5, 1024, 1024, spp_b, max_depth=8, seed=1, film=film_r, wavefront=wave)   # replicated, this rank alone
+            torch.cuda.synchronize()
+            num = float(((film_b[..., :3] - film_r[..., :3]) ** 2).mean())
+            den = float((film_r[..., :3] ** 2).mean())
+            out["cfg5_by_table"] = {"spp": spp_b, "ms": ms_b, "spp_mpix_per_s": spp_b * 1024 * 1024 / 1e6 / (ms_b * 1e-3),
+                                    "tables_per_gpu": sum(1 for p in own if p is not None),
+                                    "table_bytes_per_gpu": int(sum(p.info.table_bytes for p in own if p is not None)),
+                                    "rel_mse_vs_replicated_same_samples": num / max(den, 1e-30),
+                                    "stage_exchange_bytes_per_bounce": 48 * wave,
+                                    "ratio_to_sample_sharding": (spp_b * 1024 * 1024 / 1e6 / (ms_b * 1e-3)) / out["cfg5"]["spp_mpix_per_s"]}
+            xb.close()
         del plugs
     return out
 
 
 def main():
     args = parse()
-    if args.impl == "reference":
+    if args.cpu_legs:
+        print(json.dumps(cpu_legs()), flush=True)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)

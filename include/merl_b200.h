@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MERL_B200_ABI_VERSION 1
+#define MERL_B200_ABI_VERSION 2
 
 typedef enum merl_status {
     MERL_OK = 0,
@@ -147,9 +147,21 @@ int merl_sample(const merl_table_t* t, const float* wix, const float* wiy, const
  * .w accumulates the number of contributing queries.  Channels of invalid (negative, clamped) cells
  * receive no gradient: they are kept at zero in grad_cells4 (batches with at least as many queries
  * as the table has cells scatter unmasked and zero those channels in one pass afterwards, so
- * grad_cells4 must not be shared with gradients from other sources).  flags bit0: warp-aggregate equal cells
- * with __match_any_sync before the atomic (default on; 0 = plain per-lane RED). */
+ * grad_cells4 must not be shared with gradients from other sources).
+ * flags bit0 MERL_BWD_WARP_AGGREGATE: fold lanes of a warp that hit the same cell with __match_any_sync
+ *   before the atomic.  OFF by default in every host of this repository (0 = plain per-lane RED): on
+ *   uniformly random batches collisions inside a warp are rare and the fold costs 4 %; set it for
+ *   coherent batches (gradients of a rendered image: neighbouring pixels share cells).
+ * flags bit1 MERL_BWD_DEFER_MASK: scatter unmasked whatever the batch size and leave the validity mask
+ *   to the caller, who applies it ONCE after the last batch: merl_peerbuf_allreduce(.., table, ..)
+ *   fuses it into the multi-GPU exchange, merl_grad_apply_mask does it on one GPU.  This is the
+ *   intended form when gradients accumulate over several batches per exchange.
+ * flags bit2 MERL_BWD_CTA_AGGREGATE: coherent batches (see merl_backward notes in DESIGN.md section 5):
+ *   a per-CTA shared-memory accumulator folds the queries of a CTA that hit the same cell before one
+ *   vector RED per distinct cell and flush. */
 #define MERL_BWD_WARP_AGGREGATE 1u
+#define MERL_BWD_DEFER_MASK 2u
+#define MERL_BWD_CTA_AGGREGATE 4u
 int merl_backward(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
                   const float* wox, const float* woy, const float* woz, const float* gr,
                   const float* gg, const float* gb, const uint8_t* active, int64_t n,
@@ -159,6 +171,9 @@ int merl_backward(const merl_table_t* t, const float* wix, const float* wiy, con
  * (the .w lane of the table holds validity bits, which an optimiser must not move): what the
  * Mitsuba 3 host's dr::CustomOp hands back to Dr.Jit.  Asynchronous on `stream`. */
 int merl_grad_clear_counts(const merl_table_t* t, float* grad_cells4, merl_stream_t stream);
+/* Zero the channels of invalid (negative, clamped) cells in a gradient table that was accumulated
+ * with MERL_BWD_DEFER_MASK.  Asynchronous on `stream`. */
+int merl_grad_apply_mask(const merl_table_t* t, float* grad_cells4, merl_stream_t stream);
 
 /* ---- AoS entry points for the Mitsuba 0.6 wavefront BSDF stage --------------------------
  * wi4 / wo4: float4 per query (xyz, w ignored).  out4 = (r, g, b, pdf). */
@@ -205,6 +220,14 @@ typedef struct merl_render_params {
     float cam_pos[3], cam_target[3], cam_up[3];
     float fov_x_deg;
     float env[3];              /* constant environment radiance (RGB)                    */
+    /* By-table sharding (BASELINE config 5 "sharded by table"), the allreduce-only
+     * form: every rank traces every path of [spp_begin, spp_end) -- the SAME range on all ranks --, runs
+     * the BSDF stage only for tables m with m % table_shard_world == table_shard_rank (tables[m] of the
+     * other materials may be NULL: a rank holds only its share), and the stage outputs (48 B per path
+     * slot) are summed over the ranks through `stage_exchange` once per bounce.  Every rank ends with the
+     * full film; no film exchange.  table_shard_world <= 1: off (tables replicated, ranks split samples). */
+    int32_t table_shard_world, table_shard_rank;
+    struct merl_peerbuf* stage_exchange;   /* >= 12 * (paths per pass) floats; required when sharding */
 } merl_render_params_t;
 
 typedef struct merl_render_stats {
@@ -233,6 +256,37 @@ int merl_comm_unique_id(void* id_out /* MERL_COMM_ID_BYTES */);
 int merl_comm_create(const void* id, int nranks, int rank, int device, merl_comm_t** out);
 int merl_comm_destroy(merl_comm_t* c);
 int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_stream_t stream);
+
+/* ---- exchange buffers: ONE kernel over NVLink peer memory instead of a library allreduce -------
+ * A gradient table (or a film) that the ranks of a communicator sum in place.  merl_peerbuf_create
+ * is COLLECTIVE (every rank calls it with the same count, in the same order relative to other
+ * collectives of `c`): it allocates `count` floats (rounded up to a multiple of 4, zeroed) on the
+ * communicator's device and
+ *   MERL_XCHG_PEER (default): maps every rank's buffer into every other rank's address space (CUDA
+ *     IPC; one process per GPU, peers reachable over NVLink/NVSwitch or PCIe P2P).
+ *     merl_peerbuf_allreduce is then one persistent kernel per rank: rank r pulls slab r of all R
+ *     buffers, sums in rank order, optionally applies mask_table's validity mask, pushes the result
+ *     into slab r of all R buffers; two cross-GPU flag barriers.  All ranks end with identical bits.
+ *     No host-side state per call: capturable in a CUDA graph.
+ *   MERL_XCHG_NCCL: ncclMemAlloc + registration with the communicator (symmetric window, else
+ *     ncclCommRegister); merl_peerbuf_allreduce is ncclAllReduce in place (+ the mask pass).
+ * merl_peerbuf_allreduce(count = floats to sum, multiple of 4; mask_table = NULL or the table whose
+ * gradient this is, then count must be 4 * ncell) is asynchronous on `stream`; every rank must call it
+ * with the same count, and exchanges of one communicator must be issued in the same order everywhere.
+ * merl_peerbuf_info.status != 0: a cross-GPU barrier timed out (a rank died or skipped a call). */
+typedef struct merl_peerbuf merl_peerbuf_t;
+#define MERL_XCHG_PEER 0
+#define MERL_XCHG_NCCL 1
+typedef struct merl_peerbuf_info {
+    float* data;               /* device float[count], owned by the library */
+    int64_t count;
+    int32_t transport, nranks, rank, status;
+    char registration[64];     /* how the buffer was made visible to the other ranks */
+} merl_peerbuf_info_t;
+int merl_peerbuf_create(merl_comm_t* c, int64_t count, int transport, merl_peerbuf_t** out);
+int merl_peerbuf_destroy(merl_peerbuf_t* b);   /* collective */
+int merl_peerbuf_info(const merl_peerbuf_t* b, merl_peerbuf_info_t* out);
+int merl_peerbuf_allreduce(merl_peerbuf_t* b, int64_t count, const merl_table_t* mask_table, merl_stream_t stream);
 
 /* ---- diagnostics ------------------------------------------------------------------------ */
 const char* merl_last_error(void);

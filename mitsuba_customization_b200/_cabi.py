@@ -23,10 +23,15 @@ SYMBOLS = [
     "merl_eval_pdf_aos", "merl_sample_aos", "merl_eval_pdf_host", "merl_sample_host",
     "merl_render", "merl_set_render_graphs",
     "merl_comm_unique_id", "merl_comm_create", "merl_comm_destroy", "merl_allreduce_sum_f32",
+    "merl_grad_apply_mask",
+    "merl_peerbuf_create", "merl_peerbuf_destroy", "merl_peerbuf_info", "merl_peerbuf_allreduce",
     "merl_last_error", "merl_abi_version", "merl_launch_count", "merl_set_sample_search",
 ]
 
 BWD_WARP_AGGREGATE = 1
+BWD_DEFER_MASK = 2
+BWD_CTA_AGGREGATE = 4
+XCHG_PEER, XCHG_NCCL = 0, 1
 
 
 class MerlError(RuntimeError):
@@ -50,6 +55,11 @@ class TableInfo(C.Structure):
         ("d_cells", C.c_void_p), ("d_cdf", C.c_void_p), ("d_dens", C.c_void_p),
         ("spec_weight", C.c_float), ("smem_eval_bytes", C.c_int32), ("smem_sample_bytes", C.c_int32),
     ]
+
+
+class PeerbufInfo(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("count", C.c_int64), ("transport", C.c_int32), ("nranks", C.c_int32),
+                ("rank", C.c_int32), ("status", C.c_int32), ("registration", C.c_char * 64)]
 
 
 class FileReport(C.Structure):
@@ -107,6 +117,11 @@ def lib():
         L.merl_comm_create.argtypes = [vp, i32, i32, i32, C.POINTER(vp)]
         L.merl_comm_destroy.argtypes = [vp]
         L.merl_allreduce_sum_f32.argtypes = [vp, vp, i64, vp]
+        L.merl_grad_apply_mask.argtypes = [vp, vp, vp]
+        L.merl_peerbuf_create.argtypes = [vp, i64, i32, C.POINTER(vp)]
+        L.merl_peerbuf_destroy.argtypes = [vp]
+        L.merl_peerbuf_info.argtypes = [vp, C.POINTER(PeerbufInfo)]
+        L.merl_peerbuf_allreduce.argtypes = [vp, i64, vp, vp]
         _lib = L
     return _lib
 

@@ -313,8 +313,12 @@ class MERL:
         return bs, out[4:7]
 
     # -- differentiable backward (row A10) -----------------------------------------------------
-    def backward(self, si, wo, grad_rgb, active=True, grad_cells=None, warp_aggregate=True):
-        """grad_cells (ncell, 4) += d eval / d cells . grad_rgb; returns grad_cells."""
+    def backward(self, si, wo, grad_rgb, active=True, grad_cells=None, warp_aggregate=False, defer_mask=False,
+                 cta_aggregate=False):
+        """grad_cells (ncell, 4) += d eval / d cells . grad_rgb; returns grad_cells.
+        warp_aggregate / cta_aggregate: for coherent batches (gradients of a rendered image); off by
+        default, as in every host of this repository (include/merl_b200.h).  defer_mask: accumulate
+        unmasked, the caller applies the validity mask once (apply_grad_mask / PeerBuffer.allreduce_)."""
         wi, wo, g = _vec(si.wi, "si.wi"), _vec(wo, "wo"), _vec(grad_rgb, "grad_rgb")
         n = wi.shape[1]
         if grad_cells is None:
@@ -322,8 +326,16 @@ class MERL:
         m = _mask(active, n, wi.device)
         check(_cabi.lib().merl_backward(self._h, _ptr(wi[0]), _ptr(wi[1]), _ptr(wi[2]), _ptr(wo[0]), _ptr(wo[1]),
                                         _ptr(wo[2]), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]), _ptr(m), n,
-                                        _ptr(grad_cells), _cabi.BWD_WARP_AGGREGATE if warp_aggregate else 0,
+                                        _ptr(grad_cells),
+                                        (_cabi.BWD_WARP_AGGREGATE if warp_aggregate else 0)
+                                        | (_cabi.BWD_DEFER_MASK if defer_mask else 0)
+                                        | (_cabi.BWD_CTA_AGGREGATE if cta_aggregate else 0),
                                         _stream(wi.device)))
+        return grad_cells
+
+    def apply_grad_mask(self, grad_cells):
+        """Zero the channels of invalid cells in a gradient accumulated with defer_mask=True."""
+        check(_cabi.lib().merl_grad_apply_mask(self._h, _ptr(grad_cells), _stream(grad_cells.device)))
         return grad_cells
 
     # -- host-buffer path (scalar variants / end-to-end) ---------------------------------------

@@ -6,6 +6,7 @@
 #include <nvtx3/nvToolsExt.h>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <unistd.h>
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -23,6 +24,7 @@
 #include "../../include/merl_b200.h"
 #include "merl_kernels.cuh"
 #include "merl_render.cuh"
+#include "merl_exchange.cuh"
 
 
 using namespace merl;
@@ -70,6 +72,20 @@ static int fail(int code, const char* fmt, ...) {
         if (e_ != cudaSuccess)                                                               \
             return fail(MERL_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
+
+// No exception crosses the C boundary (include/merl_b200.h): the bodies that allocate host memory run
+// inside this guard, which turns bad_alloc / length_error / anything else into a status code.
+template <typename F> static int guarded(const char* what, F&& body) {
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        return fail(MERL_ERR_NOMEM, "%s: out of host memory", what);
+    } catch (const std::exception& e) {
+        return fail(MERL_ERR_NOMEM, "%s: %s", what, e.what());
+    } catch (...) {
+        return fail(MERL_ERR_NOMEM, "%s: unknown C++ exception", what);
+    }
+}
 
 extern "C" const char* merl_last_error(void) { return g_err.c_str(); }
 extern "C" int merl_abi_version(void) { return MERL_B200_ABI_VERSION; }
@@ -223,17 +239,21 @@ static constexpr int kMinbScale = 256 / kThreadsPerCta;   // MINB values below a
 static constexpr size_t kMaxSmemBytes = 100 * 1024;   // per-table image (edges, densities, CDF rows)
 
 template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
-    // cached per (kernel instantiation, smem size)
+    // Cached per (device, kernel instantiation, smem size): cudaFuncSetAttribute and the occupancy
+    // figure both apply to the CURRENT device only, and one process may hold tables on several.
+    struct Key { int dev; const void* fn; size_t smem; };
     static std::mutex mu;
-    static std::vector<std::pair<std::pair<const void*, size_t>, int>> cache;
+    static std::vector<std::pair<Key, int>> cache;
+    int dev = 0;
+    cudaGetDevice(&dev);
     std::lock_guard<std::mutex> lk(mu);
-    const std::pair<const void*, size_t> key((const void*)kernel, smem);
     for (auto& e : cache)
-        if (e.first == key) return e.second;
+        if (e.first.dev == dev && e.first.fn == (const void*)kernel && e.first.smem == smem) return e.second;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kThreads, smem) != cudaSuccess || nb < 1) nb = 1;
-    cache.push_back({key, nb});
+    cudaGetLastError();
+    cache.push_back({Key{dev, (const void*)kernel, smem}, nb});
     return nb;
 }
 
@@ -489,13 +509,17 @@ static int build_table(const double* planar, const merl_table_params_t* pin, int
     return MERL_OK;
 }
 
-extern "C" int merl_table_create_from_host(const double* planar_rgb, const merl_table_params_t* p, int device,
+static int merl_table_create_from_host_impl(const double* planar_rgb, const merl_table_params_t* p, int device,
                                            merl_table_t** out) {
     MERL_RANGE("merl_table_create_from_host");
     return build_table(planar_rgb, p, device, out);
 }
+extern "C" int merl_table_create_from_host(const double* planar_rgb, const merl_table_params_t* p, int device,
+                                           merl_table_t** out) {
+    return guarded("merl_table_create_from_host", [&]() -> int { return merl_table_create_from_host_impl(planar_rgb, p, device, out); });
+}
 
-extern "C" int merl_table_create_from_file(const char* path, const merl_table_params_t* pin, int device,
+static int merl_table_create_from_file_impl(const char* path, const merl_table_params_t* pin, int device,
                                            merl_table_t** out) {
     MERL_RANGE("merl_table_create_from_file");
     if (!path || !out) return fail(MERL_ERR_ARG, "NULL argument");
@@ -505,7 +529,17 @@ extern "C" int merl_table_create_from_file(const char* path, const merl_table_pa
     if (fread(dims, sizeof(int32_t), 3, f) != 3) { fclose(f); return fail(MERL_ERR_IO, "'%s': short header", path); }
     merl_table_params_t p;
     if (pin) p = *pin; else merl_table_params_default(&p);
+    // a wrong or corrupt file must fail here, before anything is sized from its header
+    if (dims[0] < 1 || dims[1] < 1 || dims[2] < 1 || dims[0] > (1 << 20) || dims[1] > (1 << 20) || dims[2] > (1 << 20)) {
+        fclose(f);
+        return fail(MERL_ERR_IO, "'%s': implausible header %d x %d x %d", path, dims[0], dims[1], dims[2]);
+    }
     if (p.nh == 0 && p.nd == 0 && p.np == 0) { p.nh = dims[0]; p.nd = dims[1]; p.np = dims[2]; }
+    if (p.nh < 2 || p.nh > kMaxNH || p.nd < 2 || p.nd > kMaxND || p.np < 2 || p.np > kMaxNP) {
+        fclose(f);
+        return fail(MERL_ERR_UNSUPPORTED, "'%s': resolution %dx%dx%d outside [2..%d]x[2..%d]x[2..%d]", path, p.nh, p.nd,
+                    p.np, kMaxNH, kMaxND, kMaxNP);
+    }
     const int64_t n = (int64_t)dims[0] * dims[1] * dims[2];
     // the public reader's check: the product of the header must equal the expected cell count
     if (n != (int64_t)p.nh * p.nd * p.np) {
@@ -513,11 +547,25 @@ extern "C" int merl_table_create_from_file(const char* path, const merl_table_pa
         return fail(MERL_ERR_IO, "'%s': header %dx%dx%d does not match the expected %dx%dx%d cells", path, dims[0],
                     dims[1], dims[2], p.nh, p.nd, p.np);
     }
+    {   // the payload must be there before it is allocated for
+        fseek(f, 0, SEEK_END);
+        const long long have = (long long)ftell(f), need = 12 + 24 * (long long)n;
+        fseek(f, 12, SEEK_SET);
+        if (have < need) {
+            fclose(f);
+            return fail(MERL_ERR_IO, "'%s': %lld bytes, a %d x %d x %d table needs %lld", path, have, dims[0], dims[1],
+                        dims[2], need);
+        }
+    }
     std::vector<double> raw((size_t)3 * n);
     const size_t got = fread(raw.data(), sizeof(double), raw.size(), f);
     fclose(f);
     if (got != raw.size()) return fail(MERL_ERR_IO, "'%s': expected %zu doubles, read %zu", path, raw.size(), got);
     return build_table(raw.data(), &p, device, out);
+}
+extern "C" int merl_table_create_from_file(const char* path, const merl_table_params_t* pin, int device,
+                                           merl_table_t** out) {
+    return guarded("merl_table_create_from_file", [&]() -> int { return merl_table_create_from_file_impl(path, pin, device, out); });
 }
 
 extern "C" int merl_table_destroy(merl_table_t* t) {
@@ -588,7 +636,7 @@ extern "C" int merl_table_download(const merl_table_t* t, float* cells4, float* 
 // table files either side of the loader: a report on a .binary file, and a
 // packed sidecar that holds the device-format table so a scene with many tables starts fast
 // ------------------------------------------------------------------------------------------
-extern "C" int merl_file_report(const char* path, merl_file_report_t* o) {
+static int merl_file_report_impl(const char* path, merl_file_report_t* o) {
     if (!path || !o) return fail(MERL_ERR_ARG, "NULL argument");
     memset(o, 0, sizeof *o);
     FILE* f = fopen(path, "rb");
@@ -632,6 +680,9 @@ extern "C" int merl_file_report(const char* path, merl_file_report_t* o) {
     fclose(f);
     return MERL_OK;
 }
+extern "C" int merl_file_report(const char* path, merl_file_report_t* o) {
+    return guarded("merl_file_report", [&]() -> int { return merl_file_report_impl(path, o); });
+}
 
 namespace {
 struct PackedHeader {
@@ -649,7 +700,7 @@ uint64_t fnv1a(const void* p, size_t n, uint64_t h) {
 }
 }  // namespace
 
-extern "C" int merl_table_save_packed(const merl_table_t* t, const char* path) {
+static int merl_table_save_packed_impl(const merl_table_t* t, const char* path) {
     if (!t || !path) return fail(MERL_ERR_ARG, "NULL argument");
     const TableDev& d = t->dev;
     std::vector<float> cells((size_t)4 * t->ncell), cdf((size_t)d.ni * (d.nh + 1));
@@ -670,8 +721,11 @@ extern "C" int merl_table_save_packed(const merl_table_t* t, const char* path) {
     if (fclose(f) != 0 || !ok) return fail(MERL_ERR_IO, "'%s': write error", path);
     return MERL_OK;
 }
+extern "C" int merl_table_save_packed(const merl_table_t* t, const char* path) {
+    return guarded("merl_table_save_packed", [&]() -> int { return merl_table_save_packed_impl(t, path); });
+}
 
-extern "C" int merl_table_create_from_packed(const char* path, int device, merl_table_t** out) {
+static int merl_table_create_from_packed_impl(const char* path, int device, merl_table_t** out) {
     MERL_RANGE("merl_table_create_from_packed");
     if (!path || !out) return fail(MERL_ERR_ARG, "NULL argument");
     FILE* f = fopen(path, "rb");
@@ -695,6 +749,9 @@ extern "C" int merl_table_create_from_packed(const char* path, int device, merl_
     if (fnv1a(cdf.data(), cdf.size() * 4, fnv1a(cells.data(), cells.size() * 4, 1469598103934665603ull)) != h.checksum)
         return fail(MERL_ERR_IO, "'%s': checksum mismatch", path);
     return build_table(nullptr, &p, device, out, cells.data(), cdf.data());
+}
+extern "C" int merl_table_create_from_packed(const char* path, int device, merl_table_t** out) {
+    return guarded("merl_table_create_from_packed", [&]() -> int { return merl_table_create_from_packed_impl(path, device, out); });
 }
 
 // ------------------------------------------------------------------------------------------
@@ -801,7 +858,7 @@ struct BackwardIn {
 };
 
 template <int AGG, int GATHER>
-static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* grad, cudaStream_t s) {
+static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* grad, cudaStream_t s, bool mask_pass) {
     const int fl = t->dev.off_dens;
     const QueryIn& q = in.q;
     const bool vec = aligned(q.wix, 16) && aligned(q.wiy, 16) && aligned(q.wiz, 16) && aligned(q.wox, 16) &&
@@ -821,7 +878,7 @@ static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* g
         const int rc = launch_op<Op, 3 * kMinbScale>(t, Op{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done, s);
         if (rc) return rc;
     }
-    if (!GATHER && n > 0) {
+    if (!GATHER && n > 0 && mask_pass) {
         backward_mask_kernel<<<t->num_sms * 8, 256, 0, s>>>(t->d_cells, grad, t->ncell);
         CUDA_TRY(cudaGetLastError());
         g_launches.fetch_add(1);
@@ -842,10 +899,15 @@ extern "C" int merl_backward(const merl_table_t* t, const float* wix, const floa
     BackwardIn in{{wix, wiy, wiz, wox, woy, woz, active}, gr, gg, gb};
     float4* grad = reinterpret_cast<float4*>(grad_cells4);
     // big batches: unmasked scatter + one mask pass over the table; small ones: per-query validity gather
-    const bool gather = n < t->ncell || !t->params.clamp_negative;
+    bool gather = n < t->ncell || !t->params.clamp_negative;
     cudaStream_t s = (cudaStream_t)stream;
-    if (flags & MERL_BWD_WARP_AGGREGATE) return gather ? run_backward<1, 1>(t, in, n, grad, s) : run_backward<1, 0>(t, in, n, grad, s);
-    return gather ? run_backward<0, 1>(t, in, n, grad, s) : run_backward<0, 0>(t, in, n, grad, s);
+    // MERL_BWD_DEFER_MASK: every query scatters unmasked whatever the batch size and the caller applies the
+    // validity mask once per exchange (merl_peerbuf_allreduce with the table, or merl_grad_apply_mask)
+    const bool defer = (flags & MERL_BWD_DEFER_MASK) != 0;
+    if (defer && t->params.clamp_negative) gather = false;
+    const bool mp = !defer;
+    if (flags & MERL_BWD_WARP_AGGREGATE) return gather ? run_backward<1, 1>(t, in, n, grad, s, mp) : run_backward<1, 0>(t, in, n, grad, s, mp);
+    return gather ? run_backward<0, 1>(t, in, n, grad, s, mp) : run_backward<0, 0>(t, in, n, grad, s, mp);
 }
 
 // hit counts out of a gradient table
@@ -895,39 +957,56 @@ extern "C" int merl_sample_aos(const merl_table_t* t, const float* wi4, const fl
 struct HostPipe {
     static constexpr int kSlots = 3;
     static constexpr int64_t kChunk = 1 << 21;
+    int64_t cap = 0;          // floats per array the slots are sized for (<= kChunk)
     cudaStream_t stream[kSlots]{};
-    float* d_in[kSlots]{};    // 6 arrays of kChunk floats
-    float* d_out[kSlots]{};   // 8 arrays of kChunk floats
+    float* d_in[kSlots]{};    // 6 arrays of cap floats
+    float* d_out[kSlots]{};   // 8 arrays of cap floats
 };
 
-static int get_pipe(merl_table* t, HostPipe** out) {
-    if (!t->pipe) {
-        HostPipe* p = new HostPipe();
-        for (int s = 0; s < HostPipe::kSlots; ++s) {
-            CUDA_TRY(cudaStreamCreateWithFlags(&p->stream[s], cudaStreamNonBlocking));
-            CUDA_TRY(cudaMalloc(&p->d_in[s], sizeof(float) * 6 * HostPipe::kChunk));
-            CUDA_TRY(cudaMalloc(&p->d_out[s], sizeof(float) * 8 * HostPipe::kChunk));
-        }
-        t->pipe = p;
+static void release_pipe(HostPipe* p) {
+    if (!p) return;
+    for (int s = 0; s < HostPipe::kSlots; ++s) {
+        if (p->stream[s]) { cudaStreamSynchronize(p->stream[s]); cudaStreamDestroy(p->stream[s]); }
+        cudaFree(p->d_in[s]);
+        cudaFree(p->d_out[s]);
     }
-    *out = static_cast<HostPipe*>(t->pipe);
+    delete p;
+}
+
+// Slots hold min(n, kChunk) queries (rounded up to a power of two >= 1024): a scalar-variant host
+// that asks for one query at a time pins 3 x 14 x 4 KB per table, not 3 x 14 x 8 MB; a later, larger
+// call grows the pipe.  Partial allocation failures release what was made.
+static int get_pipe(merl_table* t, int64_t n, HostPipe** out) {
+    int64_t want = 1024;
+    while (want < n && want < HostPipe::kChunk) want <<= 1;
+    HostPipe* p = static_cast<HostPipe*>(t->pipe);
+    if (p && p->cap >= want) { *out = p; return MERL_OK; }
+    if (p) { release_pipe(p); t->pipe = nullptr; }
+    p = new HostPipe();
+    p->cap = want;
+    for (int s = 0; s < HostPipe::kSlots; ++s) {
+        cudaError_t e = cudaStreamCreateWithFlags(&p->stream[s], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaMalloc(&p->d_in[s], sizeof(float) * 6 * want);
+        if (e == cudaSuccess) e = cudaMalloc(&p->d_out[s], sizeof(float) * 8 * want);
+        if (e != cudaSuccess) {
+            release_pipe(p);
+            return fail(e == cudaErrorMemoryAllocation ? MERL_ERR_NOMEM : MERL_ERR_CUDA, "host pipeline buffers: %s",
+                        cudaGetErrorString(e));
+        }
+    }
+    t->pipe = p;
+    *out = p;
     return MERL_OK;
 }
 
 static void free_pipe(merl_table* t) {
     if (!t || !t->pipe) return;
     DeviceGuard g(t->device);
-    HostPipe* p = static_cast<HostPipe*>(t->pipe);
-    for (int s = 0; s < HostPipe::kSlots; ++s) {
-        if (p->stream[s]) cudaStreamDestroy(p->stream[s]);
-        cudaFree(p->d_in[s]);
-        cudaFree(p->d_out[s]);
-    }
-    delete p;
+    release_pipe(static_cast<HostPipe*>(t->pipe));
     t->pipe = nullptr;
 }
 
-extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
+static int merl_eval_pdf_host_impl(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
                                   const float* wox, const float* woy, const float* woz, int64_t n, float* r,
                                   float* g, float* b, float* pdf) {
     MERL_RANGE("merl_eval_pdf_host");
@@ -938,8 +1017,8 @@ extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, cons
     DeviceGuard gd(t->device);
     std::lock_guard<std::mutex> lk(t->host_mu);
     HostPipe* p;
-    if ((rc = get_pipe(t, &p))) return rc;
-    const int64_t C = HostPipe::kChunk;
+    if ((rc = get_pipe(t, n, &p))) return rc;
+    const int64_t C = p->cap;
     const float* src[6] = {wix, wiy, wiz, wox, woy, woz};
     float* dst[4] = {r, g, b, pdf};
     int slot = 0;
@@ -959,8 +1038,13 @@ extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, cons
     for (int s = 0; s < HostPipe::kSlots; ++s) CUDA_TRY(cudaStreamSynchronize(p->stream[s]));
     return MERL_OK;
 }
+extern "C" int merl_eval_pdf_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
+                                  const float* wox, const float* woy, const float* woz, int64_t n, float* r,
+                                  float* g, float* b, float* pdf) {
+    return guarded("merl_eval_pdf_host", [&]() -> int { return merl_eval_pdf_host_impl(tc, wix, wiy, wiz, wox, woy, woz, n, r, g, b, pdf); });
+}
 
-extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
+static int merl_sample_host_impl(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
                                 const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
                                 float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe) {
     MERL_RANGE("merl_sample_host");
@@ -972,8 +1056,8 @@ extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const 
     DeviceGuard gd(t->device);
     std::lock_guard<std::mutex> lk(t->host_mu);
     HostPipe* p;
-    if ((rc = get_pipe(t, &p))) return rc;
-    const int64_t C = HostPipe::kChunk;
+    if ((rc = get_pipe(t, n, &p))) return rc;
+    const int64_t C = p->cap;
     const float* src[6] = {wix, wiy, wiz, u1, u2x, u2y};
     float* dst[8] = {wox, woy, woz, pdf, wr, wg, wb, reinterpret_cast<float*>(lobe)};
     int slot = 0;
@@ -995,6 +1079,11 @@ extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const 
     for (int s = 0; s < HostPipe::kSlots; ++s) CUDA_TRY(cudaStreamSynchronize(p->stream[s]));
     return MERL_OK;
 }
+extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const float* wiy, const float* wiz,
+                                const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
+                                float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe) {
+    return guarded("merl_sample_host", [&]() -> int { return merl_sample_host_impl(tc, wix, wiy, wiz, u1, u2x, u2y, n, wox, woy, woz, pdf, wr, wg, wb, lobe); });
+}
 
 // ------------------------------------------------------------------------------------------
 // multi-GPU exchange step: NCCL bound at run time (no link-time dependency)
@@ -1008,6 +1097,15 @@ struct NcclApi {
     int (*CommDestroy)(void* comm) = nullptr;
     int (*AllReduce)(const void* send, void* recv, size_t count, int dtype, int op, void* comm, cudaStream_t s) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
+    // optional (present in NCCL >= 2.19 / 2.27): gather of the IPC handles, registered buffers
+    int (*AllGather)(const void* send, void* recv, size_t count, int dtype, void* comm, cudaStream_t s) = nullptr;
+    int (*MemAlloc)(void** ptr, size_t size) = nullptr;
+    int (*MemFree)(void* ptr) = nullptr;
+    int (*CommRegister)(void* comm, void* buf, size_t size, void** handle) = nullptr;
+    int (*CommDeregister)(void* comm, void* handle) = nullptr;
+    int (*CommWindowRegister)(void* comm, void* buf, size_t size, void** win, int flags) = nullptr;
+    int (*CommWindowDeregister)(void* comm, void* win) = nullptr;
+    int (*GetVersion)(int* v) = nullptr;
     bool ok = false;
 };
 NcclApi* nccl_api() {
@@ -1023,6 +1121,14 @@ NcclApi* nccl_api() {
         *(void**)&api.CommDestroy = dlsym(h, "ncclCommDestroy");
         *(void**)&api.AllReduce = dlsym(h, "ncclAllReduce");
         *(void**)&api.GetErrorString = dlsym(h, "ncclGetErrorString");
+        *(void**)&api.AllGather = dlsym(h, "ncclAllGather");
+        *(void**)&api.MemAlloc = dlsym(h, "ncclMemAlloc");
+        *(void**)&api.MemFree = dlsym(h, "ncclMemFree");
+        *(void**)&api.CommRegister = dlsym(h, "ncclCommRegister");
+        *(void**)&api.CommDeregister = dlsym(h, "ncclCommDeregister");
+        *(void**)&api.CommWindowRegister = dlsym(h, "ncclCommWindowRegister");
+        *(void**)&api.CommWindowDeregister = dlsym(h, "ncclCommWindowDeregister");
+        *(void**)&api.GetVersion = dlsym(h, "ncclGetVersion");
         api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce;
     });
     return &api;
@@ -1046,7 +1152,7 @@ extern "C" int merl_comm_unique_id(void* id_out) {
     return rc ? nccl_fail("ncclGetUniqueId", rc) : MERL_OK;
 }
 
-extern "C" int merl_comm_create(const void* id, int nranks, int rank, int device, merl_comm_t** out) {
+static int merl_comm_create_impl(const void* id, int nranks, int rank, int device, merl_comm_t** out) {
     if (!id || !out || nranks < 1 || rank < 0 || rank >= nranks) return fail(MERL_ERR_ARG, "bad argument");
     NcclApi* a = nccl_api();
     if (!a->ok) return fail(MERL_ERR_UNSUPPORTED, "libnccl.so.2 not found");
@@ -1062,6 +1168,9 @@ extern "C" int merl_comm_create(const void* id, int nranks, int rank, int device
     if (rc) { delete c; return nccl_fail("ncclCommInitRank", rc); }
     *out = c;
     return MERL_OK;
+}
+extern "C" int merl_comm_create(const void* id, int nranks, int rank, int device, merl_comm_t** out) {
+    return guarded("merl_comm_create", [&]() -> int { return merl_comm_create_impl(id, nranks, rank, device, out); });
 }
 
 extern "C" int merl_comm_destroy(merl_comm_t* c) {
@@ -1081,6 +1190,276 @@ extern "C" int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count,
     DeviceGuard g(c->device);
     const int rc = a->AllReduce(buf, buf, (size_t)count, /*ncclFloat32*/ 7, /*ncclSum*/ 0, c->comm, (cudaStream_t)stream);
     return rc ? nccl_fail("ncclAllReduce", rc) : MERL_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// exchange buffers: gradient tables / films that the ranks of a communicator sum through NVLink
+// peer memory with ONE kernel (merl_exchange.cuh), or -- transport MERL_XCHG_NCCL -- through
+// ncclAllReduce on a buffer from ncclMemAlloc that is registered with the communicator (symmetric
+// window when NCCL has them, else ncclCommRegister), which makes NCCL's zero-copy / NVLS path eligible
+// ------------------------------------------------------------------------------------------
+typedef void (*XchgKernel)(const PeerView, const int64_t, const float4*, uint32_t*, int*);
+static XchgKernel xchg_kernel_for(int nranks) {
+    switch (nranks) {
+        case 1: return peer_allreduce_kernel<1, 2>;   // nothing to sum; the mask pass still runs
+        case 2: return peer_allreduce_kernel<2, 2>;
+        case 4: return peer_allreduce_kernel<4, 2>;
+        case 8: return peer_allreduce_kernel<8, 2>;
+        default: return peer_allreduce_kernel<0, 1>;
+    }
+}
+
+struct merl_peerbuf {
+    merl_comm* comm = nullptr;
+    int transport = MERL_XCHG_PEER;
+    int64_t count = 0;             // floats (multiple of 4)
+    float* d_buf = nullptr;
+    uint32_t* d_flags = nullptr;   // PEER: arrive words | epoch words
+    int* h_status = nullptr;       // PEER: pinned, mapped; set by a barrier that timed out
+    int* d_status = nullptr;
+    PeerView view{};
+    bool opened[kMaxRanks] = {};
+    int ctas_per_sm = 2, num_sms = 0;
+    void* nccl_handle = nullptr;   // NCCL: ncclCommRegister handle
+    void* nccl_window = nullptr;   // NCCL: symmetric window
+    bool nccl_alloc = false;       // d_buf came from ncclMemAlloc
+    const char* registration = "none";
+};
+
+namespace {
+struct PeerHello {
+    cudaIpcMemHandle_t data, flags;
+    int32_t num_sms, pid;
+    int64_t count;
+};
+
+// every rank contributes `bytes` bytes; out = nranks x bytes in rank order (host memory)
+int comm_allgather_bytes(merl_comm* c, const void* mine, size_t bytes, void* out) {
+    NcclApi* a = nccl_api();
+    if (c->nranks == 1) { memcpy(out, mine, bytes); return MERL_OK; }
+    if (!a->AllGather) return fail(MERL_ERR_UNSUPPORTED, "this NCCL has no ncclAllGather symbol");
+    unsigned char* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, bytes * (size_t)(c->nranks + 1)));
+    cudaError_t e = cudaMemcpy(d, mine, bytes, cudaMemcpyHostToDevice);
+    int rc = 0;
+    if (e == cudaSuccess) rc = a->AllGather(d, d + bytes, bytes, /*ncclUint8*/ 1, c->comm, nullptr);
+    if (e == cudaSuccess && !rc) e = cudaStreamSynchronize(nullptr);
+    if (e == cudaSuccess && !rc) e = cudaMemcpy(out, d + bytes, bytes * (size_t)c->nranks, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (rc) return nccl_fail("ncclAllGather", rc);
+    if (e != cudaSuccess) return fail(MERL_ERR_CUDA, "gather of the peer handles: %s", cudaGetErrorString(e));
+    return MERL_OK;
+}
+// all ranks have reached this point (and everything they enqueued on the NULL stream before has run)
+int comm_barrier(merl_comm* c) {
+    int32_t one = 1;
+    std::vector<int32_t> all((size_t)c->nranks);
+    return comm_allgather_bytes(c, &one, sizeof one, all.data());
+}
+
+void peerbuf_release(merl_peerbuf* b) {
+    if (!b) return;
+    NcclApi* a = nccl_api();
+    for (int p = 0; p < kMaxRanks; ++p)
+        if (b->opened[p]) {
+            cudaIpcCloseMemHandle(b->view.data[p]);
+            cudaIpcCloseMemHandle(b->view.flags[p]);
+        }
+    if (b->nccl_window && a->CommWindowDeregister) a->CommWindowDeregister(b->comm->comm, b->nccl_window);
+    if (b->nccl_handle && a->CommDeregister) a->CommDeregister(b->comm->comm, b->nccl_handle);
+    if (b->d_buf) { if (b->nccl_alloc) a->MemFree(b->d_buf); else cudaFree(b->d_buf); }
+    cudaFree(b->d_flags);
+    if (b->h_status) cudaFreeHost(b->h_status);
+    cudaGetLastError();
+    delete b;
+}
+}  // namespace
+
+static int merl_peerbuf_create_impl(merl_comm_t* c, int64_t count, int transport, merl_peerbuf_t** out) {
+    MERL_RANGE("merl_peerbuf_create");
+    if (!c || !out || count < 1) return fail(MERL_ERR_ARG, "bad argument");
+    if (transport != MERL_XCHG_PEER && transport != MERL_XCHG_NCCL) return fail(MERL_ERR_ARG, "unknown transport %d", transport);
+    if (c->nranks > kMaxRanks) return fail(MERL_ERR_UNSUPPORTED, "at most %d ranks", kMaxRanks);
+    NcclApi* a = nccl_api();
+    DeviceGuard g(c->device);
+    merl_peerbuf* b = new merl_peerbuf();
+    b->comm = c;
+    b->transport = transport;
+    b->count = (count + 3) & ~(int64_t)3;
+    cudaDeviceGetAttribute(&b->num_sms, cudaDevAttrMultiProcessorCount, c->device);
+    const size_t bytes = sizeof(float) * (size_t)b->count;
+    auto bail = [&](int code) { peerbuf_release(b); return code; };
+#define PB_TRY(x)                                                                                   \
+    do {                                                                                            \
+        cudaError_t e_ = (x);                                                                       \
+        if (e_ != cudaSuccess)                                                                      \
+            return bail(fail(e_ == cudaErrorMemoryAllocation ? MERL_ERR_NOMEM : MERL_ERR_CUDA, "%s: %s (%s:%d)", #x, \
+                             cudaGetErrorString(e_), __FILE__, __LINE__));                          \
+    } while (0)
+    if (transport == MERL_XCHG_NCCL) {
+        // registered buffer: NCCL can then reduce in place out of user memory (no staging copies) and,
+        // on NVSwitch systems, use the in-switch reduction with fewer SMs
+        if (a->MemAlloc && a->MemFree && a->MemAlloc((void**)&b->d_buf, bytes) == 0 && b->d_buf) {
+            b->nccl_alloc = true;
+            if (a->CommWindowRegister && a->CommWindowDeregister &&
+                a->CommWindowRegister(c->comm, b->d_buf, bytes, &b->nccl_window, /*NCCL_WIN_COLL_SYMMETRIC*/ 1) == 0 &&
+                b->nccl_window)
+                b->registration = "ncclMemAlloc + ncclCommWindowRegister(symmetric)";
+            else if (a->CommRegister && a->CommDeregister && a->CommRegister(c->comm, b->d_buf, bytes, &b->nccl_handle) == 0)
+                b->registration = "ncclMemAlloc + ncclCommRegister";
+            else
+                b->registration = "ncclMemAlloc, unregistered";
+            b->nccl_window = b->nccl_window ? b->nccl_window : nullptr;
+        } else {
+            b->d_buf = nullptr;
+            PB_TRY(cudaMalloc(&b->d_buf, bytes));
+            b->registration = "cudaMalloc, unregistered (this NCCL has no ncclMemAlloc)";
+        }
+        cudaGetLastError();
+        PB_TRY(cudaMemset(b->d_buf, 0, bytes));
+        PB_TRY(cudaDeviceSynchronize());
+        *out = b;
+        return MERL_OK;
+    }
+    // peer transport: legacy CUDA IPC needs cudaMalloc memory (not a pool, not a VMM mapping)
+    PB_TRY(cudaMalloc(&b->d_buf, bytes));
+    PB_TRY(cudaMalloc(&b->d_flags, sizeof(uint32_t) * kXchgFlagWords));
+    PB_TRY(cudaMemset(b->d_buf, 0, bytes));
+    PB_TRY(cudaMemset(b->d_flags, 0, sizeof(uint32_t) * kXchgFlagWords));
+    PB_TRY(cudaHostAlloc((void**)&b->h_status, sizeof(int), cudaHostAllocMapped));
+    *b->h_status = 0;
+    PB_TRY(cudaHostGetDevicePointer((void**)&b->d_status, b->h_status, 0));
+    PB_TRY(cudaDeviceSynchronize());
+    b->view.nranks = c->nranks;
+    b->view.rank = c->rank;
+    b->view.data[c->rank] = reinterpret_cast<float4*>(b->d_buf);
+    b->view.flags[c->rank] = b->d_flags;
+    b->registration = "CUDA IPC peer mapping";
+    {   // all CTAs of an exchange must be resident at once on every rank (they spin on each other)
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, xchg_kernel_for(c->nranks), kXchgThreads, 0) != cudaSuccess || occ < 1) occ = 1;
+        cudaGetLastError();
+        b->ctas_per_sm = std::min(2, occ);
+    }
+    if (c->nranks > 1) {
+        PeerHello me{};
+        PB_TRY(cudaIpcGetMemHandle(&me.data, b->d_buf));
+        PB_TRY(cudaIpcGetMemHandle(&me.flags, b->d_flags));
+        me.num_sms = b->num_sms;
+        me.pid = (int32_t)getpid();
+        me.count = b->count;
+        std::vector<PeerHello> all((size_t)c->nranks);
+        int rc = comm_allgather_bytes(c, &me, sizeof me, all.data());
+        if (rc) return bail(rc);
+        for (int p = 0; p < c->nranks; ++p) {
+            if (all[p].count != b->count) return bail(fail(MERL_ERR_ARG, "rank %d asked for %lld floats, this rank for %lld", p,
+                                                          (long long)all[p].count, (long long)b->count));
+            b->num_sms = std::min(b->num_sms, (int)all[p].num_sms);
+            if (p == c->rank) continue;
+            if (all[p].pid == me.pid)
+                return bail(fail(MERL_ERR_UNSUPPORTED, "peer exchange needs one process per GPU (rank %d shares this process)", p));
+            void *pd = nullptr, *pf = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&pd, all[p].data, cudaIpcMemLazyEnablePeerAccess);
+            if (e == cudaSuccess) e = cudaIpcOpenMemHandle(&pf, all[p].flags, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                if (pd) cudaIpcCloseMemHandle(pd);
+                return bail(fail(MERL_ERR_UNSUPPORTED, "cannot map rank %d's buffer (no NVLink / PCIe peer access?): %s", p,
+                                 cudaGetErrorString(e)));
+            }
+            b->view.data[p] = reinterpret_cast<float4*>(pd);
+            b->view.flags[p] = reinterpret_cast<uint32_t*>(pf);
+            b->opened[p] = true;
+        }
+        if ((rc = comm_barrier(c))) return bail(rc);   // everyone has mapped everyone before the first exchange
+    }
+#undef PB_TRY
+    *out = b;
+    return MERL_OK;
+}
+extern "C" int merl_peerbuf_create(merl_comm_t* c, int64_t count, int transport, merl_peerbuf_t** out) {
+    return guarded("merl_peerbuf_create", [&]() -> int { return merl_peerbuf_create_impl(c, count, transport, out); });
+}
+
+extern "C" int merl_peerbuf_destroy(merl_peerbuf_t* b) {
+    if (!b) return MERL_OK;
+    DeviceGuard g(b->comm->device);
+    cudaDeviceSynchronize();
+    // unmap the peers, then meet, then free: no rank frees memory another rank still has mapped
+    for (int p = 0; p < kMaxRanks; ++p)
+        if (b->opened[p]) {
+            cudaIpcCloseMemHandle(b->view.data[p]);
+            cudaIpcCloseMemHandle(b->view.flags[p]);
+            b->opened[p] = false;
+        }
+    int rc = MERL_OK;
+    if (b->transport == MERL_XCHG_PEER && b->comm->nranks > 1) rc = comm_barrier(b->comm);
+    peerbuf_release(b);
+    return rc;
+}
+
+extern "C" int merl_peerbuf_info(const merl_peerbuf_t* b, merl_peerbuf_info_t* o) {
+    if (!b || !o) return fail(MERL_ERR_ARG, "NULL argument");
+    memset(o, 0, sizeof *o);
+    o->data = b->d_buf;
+    o->count = b->count;
+    o->transport = b->transport;
+    o->nranks = b->comm->nranks;
+    o->rank = b->comm->rank;
+    o->status = b->h_status ? *reinterpret_cast<volatile int*>(b->h_status) : 0;
+    snprintf(o->registration, sizeof o->registration, "%s", b->registration);
+    return MERL_OK;
+}
+
+// grid of the exchange kernel: the same on every rank (min SM count over the ranks), all CTAs co-resident
+static int xchg_grid(const merl_peerbuf* b, int64_t n4) {
+    const int64_t per = (n4 + b->comm->nranks - 1) / b->comm->nranks;
+    int64_t want = (per + kXchgThreads - 1) / kXchgThreads;
+    const int64_t cap = std::min<int64_t>((int64_t)b->num_sms * b->ctas_per_sm, kXchgMaxCtas);
+    if (want > cap) want = cap;
+    return (int)(want < 1 ? 1 : want);
+}
+
+extern "C" int merl_peerbuf_allreduce(merl_peerbuf_t* b, int64_t count, const merl_table_t* mask_table, merl_stream_t stream) {
+    MERL_RANGE("merl_peerbuf_allreduce");
+    if (!b || count < 0 || count > b->count || (count & 3)) return fail(MERL_ERR_ARG, "count must be a multiple of 4 in [0, capacity]");
+    if (mask_table && (mask_table->device != b->comm->device || 4 * mask_table->ncell != count))
+        return fail(MERL_ERR_ARG, "mask table: other device, or count != 4 * ncell");
+    if (count == 0) return MERL_OK;
+    DeviceGuard g(b->comm->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t n4 = count / 4;
+    if (b->transport == MERL_XCHG_NCCL) {
+        if (b->comm->nranks > 1) {
+            NcclApi* a = nccl_api();
+            const int rc = a->AllReduce(b->d_buf, b->d_buf, (size_t)count, /*ncclFloat32*/ 7, /*ncclSum*/ 0, b->comm->comm, s);
+            if (rc) return nccl_fail("ncclAllReduce", rc);
+        }
+        if (mask_table) {
+            backward_mask_kernel<<<mask_table->num_sms * 8, 256, 0, s>>>(mask_table->d_cells, reinterpret_cast<float4*>(b->d_buf), n4);
+            CUDA_TRY(cudaGetLastError());
+            g_launches.fetch_add(1);
+        }
+        return MERL_OK;
+    }
+    if (*reinterpret_cast<volatile int*>(b->h_status))
+        return fail(MERL_ERR_CUDA, "an earlier peer exchange timed out waiting for another rank; the buffer is unusable");
+    const float4* mask = mask_table ? mask_table->d_cells : nullptr;
+    uint32_t* epoch = b->d_flags + kXchgMaxCtas * kMaxRanks;
+    const int grid = xchg_grid(b, n4);
+    xchg_kernel_for(b->comm->nranks)<<<grid, kXchgThreads, 0, s>>>(b->view, n4, mask, epoch, b->d_status);
+    CUDA_TRY(cudaGetLastError());
+    g_launches.fetch_add(1);
+    return MERL_OK;
+}
+
+extern "C" int merl_grad_apply_mask(const merl_table_t* t, float* grad_cells4, merl_stream_t stream) {
+    if (!t || !grad_cells4) return fail(MERL_ERR_ARG, "NULL argument");
+    if ((uintptr_t)grad_cells4 & 15) return fail(MERL_ERR_ARG, "grad_cells4 must be 16-byte aligned");
+    DeviceGuard g(t->device);
+    backward_mask_kernel<<<t->num_sms * 8, 256, 0, (cudaStream_t)stream>>>(t->d_cells, reinterpret_cast<float4*>(grad_cells4), t->ncell);
+    CUDA_TRY(cudaGetLastError());
+    g_launches.fetch_add(1);
+    return MERL_OK;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1180,7 +1559,7 @@ extern "C" int merl_set_render_graphs(int on) {
     return MERL_OK;
 }
 
-extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres, int nspheres,
+static int merl_render_impl(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres, int nspheres,
                            const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out,
                            merl_stream_t stream_) {
     MERL_RANGE("merl_render");
@@ -1191,14 +1570,25 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         p->spp_end < p->spp_begin || p->spp_end > p->spp_total)
         return fail(MERL_ERR_ARG, "bad render parameters");
     if (!aligned(film4, 16)) return fail(MERL_ERR_ARG, "film4 must be 16-byte aligned");
+    // by-table sharding: this rank evaluates tables m with m % own_world == own_rank only
+    const int own_world = p->table_shard_world > 1 ? p->table_shard_world : 1;
+    const int own_rank = own_world > 1 ? p->table_shard_rank : 0;
+    if (own_world > 1 && (own_rank < 0 || own_rank >= own_world || !p->stage_exchange))
+        return fail(MERL_ERR_ARG, "by-table sharding needs table_shard_rank in [0, world) and a stage_exchange buffer");
+    const merl_table* t0 = nullptr;
     for (int k = 0; k < ntables; ++k) {
-        if (!tables[k]) return fail(MERL_ERR_ARG, "table %d is NULL", k);
-        if (tables[k]->device != tables[0]->device) return fail(MERL_ERR_ARG, "all tables must live on one device");
+        const bool mine = k % own_world == own_rank;
+        if (!tables[k]) {
+            if (mine) return fail(MERL_ERR_ARG, "table %d is NULL", k);
+            continue;
+        }
+        if (!t0) t0 = tables[k];
+        if (tables[k]->device != t0->device) return fail(MERL_ERR_ARG, "all tables must live on one device");
     }
+    if (!t0) return fail(MERL_ERR_ARG, "this rank owns no table");
     for (int k = 0; k < nspheres; ++k)
         if (spheres[k].material < 0 || spheres[k].material >= ntables || !(spheres[k].radius > 0.f))
             return fail(MERL_ERR_ARG, "sphere %d: bad material or radius", k);
-    const merl_table* t0 = tables[0];
     DeviceGuard guard(t0->device);
     cudaStream_t s = (cudaStream_t)stream_;
 
@@ -1223,6 +1613,14 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     int64_t cap = p->wavefront > 0 ? p->wavefront : (1 << 23);   // 8 Mi paths: 2 GB of workspace, kept in the pool
     if (cap > total) cap = total;
     cap = (cap + 255) & ~(int64_t)255;
+    if (own_world > 1) {
+        merl_peerbuf* xb = p->stage_exchange;
+        if (xb->comm->device != t0->device || xb->comm->nranks != own_world || xb->comm->rank != own_rank)
+            return fail(MERL_ERR_ARG, "stage_exchange belongs to another device / communicator shape");
+        if (xb->count < 12 * cap)
+            return fail(MERL_ERR_ARG, "stage_exchange holds %lld floats, a pass of %lld paths needs %lld", (long long)xb->count,
+                        (long long)cap, (long long)(12 * cap));
+    }
 
     // one stream-ordered workspace: path state, stage buffers, sort scratch, scene
     const size_t nf4 = 6, ni = 4;   // path state: six float4 and four int arrays
@@ -1299,6 +1697,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     std::vector<TableDev> ht(ntables);
     int img_floats_eval = 0, img_floats_full = 0;
     for (int k = 0; k < ntables; ++k) {
+        if (!tables[k]) { ht[k] = TableDev{}; continue; }   // another rank's table (by-table sharding)
         ht[k] = tables[k]->dev;
         img_floats_eval = std::max(img_floats_eval, ht[k].image_eval_floats);
         img_floats_full = std::max(img_floats_full, ht[k].image_full_floats);
@@ -1309,6 +1708,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     const int grid_f = t0->num_sms * blocks_per_sm(stream_multi_kernel<SampleAosOp, 3 * kMinbScale>, (size_t)img_f + kQueueBytes);
     int rc = MERL_OK;
     int64_t launches = 0;
+    RenderSide* forked = nullptr;   // set once work may have been enqueued on the side stream
 #define RT_TRY(x)                                                                                  \
     do {                                                                                           \
         cudaError_t e_ = (x);                                                                      \
@@ -1336,6 +1736,8 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     // replayed npasses times.  Capture needs a non-legacy stream, so the work runs on a side
     // stream that is forked from and joined back into the caller's stream with events: the call
     // stays asynchronous and ordered on `stream`.
+    bool xchg_failed = false;
+    const int64_t launches_before = g_launches.load();
     auto enqueue_pass = [&](cudaStream_t q) {
         // depth 0: camera rays and their first intersection in one kernel over the whole pass; its
         // hits form the depth-0 live list.  Every other kernel walks a live list (grid-stride over
@@ -1353,14 +1755,25 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
                                               d_nlive + nxt, d_nq);
             rt_scatter_kernel<<<g, 256, 2 * sizeof(int) * ntables, q>>>(P, A, B, d_pass, d_cursor, ntables, L);
             stream_multi_kernel<EvalPdfAosOp, 4 * kMinbScale><<<grid_e, kThreads, (size_t)img_e + kQueueBytes, q>>>(
-                d_tabs, ntables, d_seg, d_items, EvalPdfAosOp{B.wi4, B.woe4, B.fe4}, img_e);
+                d_tabs, ntables, d_seg, d_items, EvalPdfAosOp{B.wi4, B.woe4, B.fe4}, img_e, own_world, own_rank);
             stream_multi_kernel<SampleAosOp, 3 * kMinbScale><<<grid_f, kThreads, (size_t)img_f + kQueueBytes, q>>>(
-                d_tabs, ntables, d_seg, d_items, SampleAosOp{B.wi4, B.u4, B.wos4, B.w4}, img_f);
-            rt_shade_kernel<<<g, 256, 0, q>>>(R, P, B, d_seg + ntables, film, L);
+                d_tabs, ntables, d_seg, d_items, SampleAosOp{B.wi4, B.u4, B.wos4, B.w4}, img_f, own_world, own_rank);
+            if (own_world > 1) {
+                // this rank's share of the stage outputs -> path order in the exchange buffer, summed over
+                // the ranks (every entry has exactly one non-zero contributor), shaded from there
+                float4* x4 = reinterpret_cast<float4*>(p->stage_exchange->d_buf);
+                const StageBuf O{nullptr, nullptr, nullptr, x4, x4 + cap, x4 + 2 * cap};
+                cudaMemsetAsync(x4, 0, (size_t)cap * 48, q);
+                rt_unsort_kernel<<<g, 256, 0, q>>>(P, B, O, d_seg + ntables, own_world, own_rank);
+                if (merl_peerbuf_allreduce(p->stage_exchange, 12 * cap, nullptr, q) != MERL_OK) xchg_failed = true;
+                rt_shade_kernel<<<g, 256, 0, q>>>(R, P, O, d_seg + ntables, film, L, 1);
+            } else {
+                rt_shade_kernel<<<g, 256, 0, q>>>(R, P, B, d_seg + ntables, film, L, 0);
+            }
         }
         rt_advance_kernel<<<1, 1, 0, q>>>(d_pass, (long long)total, (int)cap, d_nlive);
     };
-    const int64_t per_pass = 2 + 6 * (int64_t)p->max_depth;
+    const int64_t per_pass = 2 + (own_world > 1 ? 8 : 6) * (int64_t)p->max_depth;
     // (a caller that is itself capturing `stream` gets the plain launches: they become part of its graph)
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) { cudaGetLastError(); cap_status = cudaStreamCaptureStatusNone; }
@@ -1371,6 +1784,7 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         side->reap();
         RT_TRY(cudaEventRecord(side->fork, s));
         RT_TRY(cudaStreamWaitEvent(side->stream, side->fork, 0));
+        forked = side;
         cudaGraph_t graph = nullptr;
         RT_TRY(cudaStreamBeginCapture(side->stream, cudaStreamCaptureModeThreadLocal));
         enqueue_pass(side->stream);
@@ -1390,12 +1804,14 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
         for (int64_t k = 0; k < npasses; ++k) RT_TRY(cudaGraphLaunch(side->exec, side->stream));
         RT_TRY(cudaEventRecord(side->join, side->stream));
         RT_TRY(cudaStreamWaitEvent(s, side->join, 0));
+        forked = nullptr;   // joined
     } else {
         for (int64_t k = 0; k < npasses; ++k) enqueue_pass(s);
         RT_TRY(cudaGetLastError());
     }
+    if (xchg_failed) { rc = MERL_ERR_CUDA; goto done; }   // (message set by merl_peerbuf_allreduce)
     launches = npasses * per_pass;
-    g_launches.fetch_add(launches);
+    g_launches.fetch_add(launches - (g_launches.load() - launches_before));   // (exchanges enqueued above counted themselves)
     if (stats_out) {
         unsigned long long nq = 0;
         RT_TRY(cudaMemcpyAsync(&nq, d_nq, 8, cudaMemcpyDeviceToHost, s));
@@ -1405,6 +1821,19 @@ extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const
     }
 done:
 #undef RT_TRY
+    if (forked) {
+        // error after the fork: graph launches may still be queued on the side stream and they use the
+        // workspace, so `s` must wait for them before the stream-ordered free below
+        if (cudaEventRecord(forked->join, forked->stream) != cudaSuccess ||
+            cudaStreamWaitEvent(s, forked->join, 0) != cudaSuccess)
+            cudaStreamSynchronize(forked->stream);
+        cudaGetLastError();
+    }
     cudaFreeAsync(ws, s);
     return rc;
+}
+extern "C" int merl_render(const merl_table_t* const* tables, int ntables, const merl_sphere_t* spheres, int nspheres,
+                           const merl_render_params_t* p, float* film4, merl_render_stats_t* stats_out,
+                           merl_stream_t stream_) {
+    return guarded("merl_render", [&]() -> int { return merl_render_impl(tables, ntables, spheres, nspheres, p, film4, stats_out, stream_); });
 }

@@ -1,0 +1,159 @@
+// merl_exchange.cuh -- the multi-GPU exchange step as ONE kernel over NVLink peer memory (sm_100a).
+//
+// the backward keeps a private fp32 gradient table per GPU and sums them once; a
+// renderer sums its film the same way.  Round 1 called ncclAllReduce for that: 23.3 MB took 0.122 ms
+// on 8 GPUs (about 334 GB/s of bus bandwidth), as long as the scatter it follows.  Here every rank's
+// buffer is mapped into every other rank's address space (CUDA IPC over NVLink / NVSwitch) and one
+// persistent kernel per rank does the whole exchange:
+//
+//   barrier A   all ranks have entered the kernel, i.e. their producers (scatter / render) are done
+//   reduce      rank r owns slab r = elements [r n/R, (r+1) n/R): it PULLS that slab from all R buffers
+//               (16-byte ld.relaxed.sys, R loads in flight per thread), sums them in rank order,
+//               optionally applies the table's validity mask (backward_mask_kernel's job, fused: the
+//               mask pass now touches 1/R of the table per GPU), and
+//   broadcast   PUSHES the result into slab r of all R buffers (st.relaxed.sys: fire and forget)
+//   barrier B   every push into this rank's buffer has landed; nobody still reads it
+//
+// Only the CTA with the same index on the owning rank ever touches a given element between the two
+// barriers, so no barrier is needed between reduce and broadcast, and every rank ends with the SAME
+// bits (one rank computes each sum).  NVLink is full duplex: pulls (inbound data) and pushes (outbound
+// data) of different ranks overlap.  Bytes per GPU and direction: (R-1)/R of the buffer each way.
+//
+// Cross-GPU barrier: CTA i of rank r writes the epoch into word [i][r] of every peer's flag block
+// (st.release.sys after a system fence) and spins on its own words [i][*] (ld.acquire.sys).  Epochs
+// only grow, live in device memory (epoch[i], advanced by the kernel itself), so the kernel has no
+// host-side state and can be captured in a CUDA graph.  All CTAs of the grid must be co-resident on
+// every rank: the host sizes the grid from the occupancy API and the same formula on every rank.  A
+// spin that exceeds ~4 s sets a sticky status word instead of hanging the GPU.
+// Included exactly once, by merl_b200.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace merl {
+
+constexpr int kMaxRanks = 16;
+constexpr int kXchgThreads = 256;
+constexpr int kXchgMaxCtas = 1024;
+constexpr int kXchgFlagWords = kXchgMaxCtas * kMaxRanks + kXchgMaxCtas;   // arrive[cta][src rank] | epoch[cta]
+constexpr long long kXchgTimeoutCycles = 8000000000ll;                          // ~4 s at 1.9 GHz
+
+struct PeerView {
+    float4* data[kMaxRanks];       // rank p's buffer in THIS process's address space (own: the local pointer)
+    uint32_t* flags[kMaxRanks];    // rank p's flag block
+    int nranks, rank;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_peer(float4* p, const float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+// CTA `cta` of every rank meets here.  Every thread fences its own earlier peer stores first.
+__device__ __forceinline__ void xchg_barrier(const PeerView& pv, const int cta, const uint32_t epoch, int* status) {
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < pv.nranks) {
+        const int p = threadIdx.x;
+        st_release_sys(pv.flags[p] + cta * kMaxRanks + pv.rank, epoch);
+        const uint32_t* mine = pv.flags[pv.rank] + cta * kMaxRanks + p;
+        const long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+            if (clock64() - t0 > kXchgTimeoutCycles) { *reinterpret_cast<volatile int*>(status) = 1; break; }   // host-mapped word
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 mask_cell(float4 g, const float bits) {
+    const int m = (int)bits;
+    if (!(m & 1)) g.x = 0.f;
+    if (!(m & 2)) g.y = 0.f;
+    if (!(m & 4)) g.z = 0.f;
+    return g;
+}
+
+// NR > 0: number of ranks known at compile time (all R loads of an element in flight at once);
+// NR == 0: any rank count, loads issued in a loop.
+template <int NR, int UNROLL>
+__global__ void __launch_bounds__(kXchgThreads) peer_allreduce_kernel(const PeerView pv, const int64_t n4,
+                                                                      const float4* __restrict__ mask_cells,
+                                                                      uint32_t* __restrict__ epoch_words,
+                                                                      int* __restrict__ status) {
+    __shared__ uint32_t e_s;
+    const int cta = blockIdx.x;
+    if (threadIdx.x == 0) e_s = epoch_words[cta];
+    __syncthreads();
+    const uint32_t e0 = e_s;
+    const int R = NR > 0 ? NR : pv.nranks;
+    xchg_barrier(pv, cta, e0 + 1u, status);
+    const int64_t per = (n4 + R - 1) / R;
+    const int64_t lo = min((int64_t)pv.rank * per, n4), hi = min(lo + per, n4);
+    const int64_t step = (int64_t)gridDim.x * kXchgThreads;
+    for (int64_t i0 = lo + (int64_t)cta * kXchgThreads + threadIdx.x; i0 < hi; i0 += step * UNROLL) {
+        float4 acc[UNROLL];
+        if (NR > 0) {
+            float4 v[UNROLL][NR > 0 ? NR : 1];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const int64_t i = i0 + u * step;
+#pragma unroll
+                for (int p = 0; p < NR; ++p)
+                    if (i < hi) v[u][p] = ld_peer(pv.data[p] + i);
+            }
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                acc[u] = v[u][0];
+#pragma unroll
+                for (int p = 1; p < NR; ++p) {
+                    acc[u].x += v[u][p].x; acc[u].y += v[u][p].y; acc[u].z += v[u][p].z; acc[u].w += v[u][p].w;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const int64_t i = i0 + u * step;
+                acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i < hi) {
+                    acc[u] = ld_peer(pv.data[0] + i);
+                    for (int p = 1; p < R; ++p) {
+                        const float4 v = ld_peer(pv.data[p] + i);
+                        acc[u].x += v.x; acc[u].y += v.y; acc[u].z += v.z; acc[u].w += v.w;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const int64_t i = i0 + u * step;
+            if (i >= hi) continue;
+            if (mask_cells) acc[u] = mask_cell(acc[u], __ldg(&reinterpret_cast<const float*>(mask_cells)[4 * i + 3]));
+            if (NR > 0) {
+#pragma unroll
+                for (int p = 0; p < NR; ++p) st_peer(pv.data[p] + i, acc[u]);
+            } else {
+                for (int p = 0; p < R; ++p) st_peer(pv.data[p] + i, acc[u]);
+            }
+        }
+    }
+    xchg_barrier(pv, cta, e0 + 2u, status);
+    if (threadIdx.x == 0) epoch_words[cta] = e0 + 2u;
+}
+
+}  // namespace merl

@@ -491,9 +491,11 @@ __device__ __forceinline__ bool shade_one(const RenderDev& R, const PathState& P
 
 // One thread per BSDF-stage slot (the live queries of this bounce, nq = seg_off[ntables]); paths
 // that continue are appended to the next bounce's live list (cta_append).
+// by_path: the stage outputs are indexed by path (by-table sharding: they come out of the per-bounce
+// exchange in path order, because slot order differs between ranks), else by slot.
 __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const PathState P, const StageBuf S,
                                                        const int* __restrict__ nq_ptr, float4* __restrict__ film,
-                                                       const LiveList L) {
+                                                       const LiveList L, const int by_path) {
     __shared__ int s_warp[kAppendWarps];
     const int nq = *nq_ptr;
     for (int s0 = blockIdx.x * blockDim.x; s0 < nq; s0 += gridDim.x * blockDim.x) {   // CTA-uniform trip count
@@ -503,7 +505,7 @@ __global__ void __launch_bounds__(256) rt_shade_kernel(const RenderDev R, const 
         if (slot < nq) {
             i = P.slot[slot];
             MERL_CHECK(i >= 0 && P.pixel[i] >= 0 && P.pixel[i] < R.width * R.height);
-            go = shade_one(R, P, S, slot, i, film);
+            go = shade_one(R, P, S, by_path ? i : slot, i, film);
         }
         const int dst = cta_append(go, L.count_out, s_warp);
         MERL_CHECK(!go || (dst >= 0 && dst < nq));
@@ -538,6 +540,21 @@ __device__ __forceinline__ bool shade_one(const RenderDev& R, const PathState& P
     return true;
 }
 
+// ---- by-table sharding: stage outputs of the tables THIS rank owns, from
+// their material-sorted slots back to path order, into the exchange buffer (zeroed before; the other
+// ranks fill in the rest, one sum per bounce makes every rank's copy complete)
+__global__ void __launch_bounds__(256) rt_unsort_kernel(const PathState P, const StageBuf B, const StageBuf O,
+                                                        const int* __restrict__ nq_ptr, const int own_world,
+                                                        const int own_rank) {
+    const int nq = *nq_ptr;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < nq; slot += gridDim.x * blockDim.x) {
+        const int m = (int)B.wi4[slot].w;
+        if (m % own_world != own_rank) continue;
+        const int i = P.slot[slot];
+        O.fe4[i] = B.fe4[slot]; O.wos4[i] = B.wos4[slot]; O.w4[i] = B.w4[slot];
+    }
+}
+
 // ---- BSDF stage over several tables: work items (one table, <= chunk queries) are dealt to the CTAs
 // in contiguous blocks, so a CTA restages the table image only when its next item is another table --
 template <typename Op, int MINB>
@@ -545,7 +562,8 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_multi_kernel(cons
                                                                             const int ntables,
                                                                             const int* __restrict__ seg_off,
                                                                             const int* __restrict__ item_off,
-                                                                            const Op op, const int image_bytes) {
+                                                                            const Op op, const int image_bytes,
+                                                                            const int own_world, const int own_rank) {
     extern __shared__ float4 smem4[];
     __shared__ TableDev t;
     float* smem = reinterpret_cast<float*>(smem4);
@@ -561,6 +579,7 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_multi_kernel(cons
     int staged = -1;
     for (int item = i0; item < i1; ++item) {
         while (item_off[m + 1] <= item) ++m;
+        if (own_world > 1 && m % own_world != own_rank) continue;   // by-table sharding: another rank's table
         const int a = seg_off[m] + (item - item_off[m]) * chunk, b = min(a + chunk, seg_off[m + 1]);
         if (m != staged) {
             __syncthreads();   // previous table fully processed (queues flushed) before the image changes

@@ -32,7 +32,9 @@ def shard_bounds(n: int, world: int, rank: int, align: int = 4) -> Tuple[int, in
 
 
 def table_owner(table_id: int, world: int) -> int:
-    """By-table sharding for multi-material scenes (BASELINE config 5): round-robin owner."""
+    """By-table sharding for multi-material scenes (BASELINE config 5): round-robin owner.  The same
+    rule as merl_render's by-table variant (merl_render_params_t.table_shard_*: table m is evaluated
+    by rank m % world), so a host can tell which tables a rank must hold."""
     return table_id % world
 
 
@@ -84,6 +86,58 @@ class Comm:
         h, self._h = self._h, None
         if h:
             check(_cabi.lib().merl_comm_destroy(h))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PeerBuffer:
+    """An exchange buffer of `count` floats on this rank's GPU (merl_peerbuf_*): the ranks of `comm` sum
+    it in place with ONE kernel over NVLink peer memory (transport "peer", default) or with ncclAllReduce
+    on a buffer registered with NCCL (transport "nccl").  Creation and destruction are collective.
+    `tensor(shape)` is a zero-copy torch view of the library-owned memory."""
+
+    def __init__(self, comm: Comm, count: int, transport: str = "peer"):
+        self.comm = comm
+        self._h = C.c_void_p()
+        kind = {"peer": _cabi.XCHG_PEER, "nccl": _cabi.XCHG_NCCL}[transport]
+        check(_cabi.lib().merl_peerbuf_create(comm._h, int(count), kind, C.byref(self._h)))
+        self.info = _cabi.PeerbufInfo()
+        check(_cabi.lib().merl_peerbuf_info(self._h, C.byref(self.info)))
+        self.count = int(self.info.count)
+        self.transport = transport
+        self.registration = self.info.registration.decode(errors="replace")
+        self.device = torch.device("cuda", comm.device)
+
+    def tensor(self, shape=None) -> torch.Tensor:
+        from .bsdf import _DevArray
+        shape = (self.count,) if shape is None else tuple(shape)
+        n = 1
+        for d in shape:
+            n *= int(d)
+        if n > self.count:
+            raise MerlError(f"view of {n} floats exceeds the buffer's {self.count}")
+        return torch.as_tensor(_DevArray(self.info.data, shape), device=self.device)
+
+    def allreduce_(self, count: Optional[int] = None, mask_plug=None) -> None:
+        """Sum the first `count` floats (default: all) over the ranks, in place, on torch's current stream.
+        mask_plug: the plugin whose table gradient this is (count = 4 * ncell): the validity mask of a
+        deferred-mask backward is applied inside the exchange."""
+        count = self.count if count is None else int(count)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        check(_cabi.lib().merl_peerbuf_allreduce(self._h, count, mask_plug._h if mask_plug is not None else None, stream))
+
+    def status(self) -> int:
+        check(_cabi.lib().merl_peerbuf_info(self._h, C.byref(self.info)))
+        return int(self.info.status)
+
+    def close(self):
+        h, self._h = self._h, None
+        if h:
+            check(_cabi.lib().merl_peerbuf_destroy(h))
 
     def __del__(self):
         try:

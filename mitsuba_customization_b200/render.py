@@ -27,7 +27,8 @@ class _Params(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp_total", C.c_int32), ("spp_begin", C.c_int32),
                 ("spp_end", C.c_int32), ("max_depth", C.c_int32), ("wavefront", C.c_int32), ("reserved", C.c_int32),
                 ("seed", C.c_uint64), ("cam_pos", C.c_float * 3), ("cam_target", C.c_float * 3),
-                ("cam_up", C.c_float * 3), ("fov_x_deg", C.c_float), ("env", C.c_float * 3)]
+                ("cam_up", C.c_float * 3), ("fov_x_deg", C.c_float), ("env", C.c_float * 3),
+                ("table_shard_world", C.c_int32), ("table_shard_rank", C.c_int32), ("stage_exchange", C.c_void_p)]
 
 
 class _Stats(C.Structure):
@@ -65,20 +66,26 @@ def grid_scene(bsdfs, nx=10, ny=10, spacing=2.2) -> Scene:
 
 def render(scene: Scene, width: int, height: int, spp: int, max_depth: int = 8, seed: int = 1,
            spp_range: Optional[Tuple[int, int]] = None, film: Optional[torch.Tensor] = None, wavefront: int = 0,
-           want_stats: bool = False):
+           want_stats: bool = False, table_shard: Optional[Tuple[int, int]] = None, stage_exchange=None):
     """Adds this call's samples to `film` ((height, width, 4) float32 CUDA, zeroed when None) and
-    returns it (and the stats when asked; asking synchronises the stream)."""
-    dev = scene.bsdfs[0].device
+    returns it (and the stats when asked; asking synchronises the stream).
+
+    table_shard = (world, rank) + stage_exchange (a distributed.PeerBuffer of >= 12 * paths-per-pass
+    floats): the by-table variant -- every rank traces the same samples, evaluates only the tables
+    k % world == rank (scene.bsdfs[k] may be None for the others) and the stage outputs are summed
+    over the ranks once per bounce; every rank ends with the full film."""
+    dev = next(b for b in scene.bsdfs if b is not None).device
     if film is None:
         film = torch.zeros(height, width, 4, dtype=torch.float32, device=dev)
     if film.shape != (height, width, 4) or film.dtype != torch.float32 or not film.is_contiguous():
         raise MerlError("film must be a contiguous (height, width, 4) float32 CUDA tensor")
-    handles = (C.c_void_p * len(scene.bsdfs))(*[b._h for b in scene.bsdfs])
+    handles = (C.c_void_p * len(scene.bsdfs))(*[(b._h if b is not None else None) for b in scene.bsdfs])
     sph = (_Sphere * len(scene.spheres))(*[_Sphere(s[0], s[1], s[2], s[3], int(s[4])) for s in scene.spheres])
     b, e = spp_range if spp_range is not None else (0, spp)
     p = _Params(width, height, spp, b, e, max_depth, wavefront, 0, seed, (C.c_float * 3)(*scene.cam_pos),
                 (C.c_float * 3)(*scene.cam_target), (C.c_float * 3)(*scene.cam_up), scene.fov_x_deg,
-                (C.c_float * 3)(*scene.env))
+                (C.c_float * 3)(*scene.env), table_shard[0] if table_shard else 0, table_shard[1] if table_shard else 0,
+                stage_exchange._h if stage_exchange is not None else None)
     st = _Stats()
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     check(_cabi.lib().merl_render(handles, len(scene.bsdfs), sph, len(scene.spheres), C.byref(p),

@@ -34,7 +34,7 @@ def test_library_is_sm100a_only(built_lib):
 
 def test_abi_version_and_defaults(built_lib):
     from mitsuba_customization_b200 import _cabi
-    assert built_lib.merl_abi_version() == 1
+    assert built_lib.merl_abi_version() == 2
     p = _cabi.default_params()
     assert (p.nh, p.nd, p.np, p.theta_h_sqrt, p.ni) == (90, 90, 180, 1, 32)
     np.testing.assert_allclose(list(p.scale), [1 / 1500, 1.15 / 1500, 1.66 / 1500])
@@ -44,14 +44,17 @@ def test_struct_layouts_match_header(built_lib):
     """ctypes mirrors are laid out exactly as the C structs (sizes from a tiny C probe)."""
     import subprocess
     import tempfile
-    src = '#include "merl_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu\\n", sizeof(merl_table_params_t), sizeof(merl_table_info_t));return 0;}\n'
+    src = ('#include "merl_b200.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu\\n", '
+           'sizeof(merl_table_params_t), sizeof(merl_table_info_t), sizeof(merl_render_params_t), '
+           'sizeof(merl_peerbuf_info_t), sizeof(merl_file_report_t));return 0;}\n')
     with tempfile.TemporaryDirectory() as d:
         open(os.path.join(d, "p.c"), "w").write(src)
         subprocess.run(["/usr/bin/gcc", "-I", os.path.join(ROOT, "include"), os.path.join(d, "p.c"), "-o",
                         os.path.join(d, "p")], check=True)
-        a, b = (int(x) for x in subprocess.run([os.path.join(d, "p")], capture_output=True, text=True).stdout.split())
-    from mitsuba_customization_b200 import _cabi
+        a, b, c, e, f = (int(x) for x in subprocess.run([os.path.join(d, "p")], capture_output=True, text=True).stdout.split())
+    from mitsuba_customization_b200 import _cabi, render
     assert C.sizeof(_cabi.TableParams) == a and C.sizeof(_cabi.TableInfo) == b
+    assert C.sizeof(render._Params) == c and C.sizeof(_cabi.PeerbufInfo) == e and C.sizeof(_cabi.FileReport) == f
 
 
 def test_argument_errors_without_gpu(built_lib):
@@ -60,6 +63,9 @@ def test_argument_errors_without_gpu(built_lib):
     rc = built_lib.merl_table_create_from_file(b"/nonexistent/file.binary", None, 0, C.byref(h))
     assert rc == -2 and b"cannot open" in built_lib.merl_last_error()
     assert built_lib.merl_set_sample_search(7) == -1
+    assert built_lib.merl_peerbuf_create(None, 16, 0, C.byref(h)) == -1
+    assert built_lib.merl_peerbuf_allreduce(None, 16, None, None) == -1
+    assert built_lib.merl_grad_apply_mask(None, None, None) == -1
     assert built_lib.merl_bins(None, None, None, None, None, None, None, None, 4, None, None) == -1
     with pytest.raises(_cabi.MerlError):
         _cabi.check(-1)
@@ -102,3 +108,22 @@ def test_header_is_plain_c(tmp_path):
                         f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     assert subprocess.run([str(exe)]).returncode == 0        # defaults and diagnostics work without a GPU
+
+
+def test_corrupt_file_header_is_an_error_not_an_exception(built_lib, tmp_path):
+    """A header that multiplies to an absurd cell count must come back as a status code before anything
+    is allocated for it (bad_alloc used to escape the extern "C" boundary)."""
+    h = C.c_void_p()
+    from mitsuba_customization_b200 import _cabi
+    p = _cabi.default_params()
+    p.nh = p.nd = p.np = 0                      # customized_measurment: resolution from the header
+    bad = tmp_path / "huge.binary"
+    bad.write_bytes(np.array([1 << 20, 1 << 20, 1 << 20], dtype=np.int32).tobytes() + b"\0" * 64)
+    assert built_lib.merl_table_create_from_file(str(bad).encode(), C.byref(p), 0, C.byref(h)) in (-2, -5)
+    neg = tmp_path / "neg.binary"
+    neg.write_bytes(np.array([-3, 90, 180], dtype=np.int32).tobytes())
+    assert built_lib.merl_table_create_from_file(str(neg).encode(), C.byref(p), 0, C.byref(h)) == -2
+    short = tmp_path / "short.binary"            # plausible header, payload missing
+    short.write_bytes(np.array([64, 96, 192], dtype=np.int32).tobytes() + b"\0" * 1000)
+    rc = built_lib.merl_table_create_from_file(str(short).encode(), C.byref(p), 0, C.byref(h))
+    assert rc == -2 and b"needs" in built_lib.merl_last_error()

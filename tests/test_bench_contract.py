@@ -32,3 +32,29 @@ def test_gpu_arm_has_no_cpu_fallback():
         pytest.skip("a GPU is present")
     r = _run("--steps", "1", "--warmup", "1", timeout=300)
     assert r.returncode != 0 and "CUDA" in (r.stderr + r.stdout)
+
+
+def test_reference_arm_ignores_torchrun_thread_cap(built_lib):
+    """torchrun exports OMP_NUM_THREADS=1 to its workers; the reference arm must still use every host thread
+    of its affinity mask, so that the driver's ratio means the same at every N."""
+    env = dict(os.environ, OMP_NUM_THREADS="1", RANK="0", WORLD_SIZE="2")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+                        "--warmup", "1"], capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0)) and line["n_gpus"] == 2
+    env["RANK"] = "1"                          # the other ranks exit 0 without work
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_cpu_legs_subprocess_reports_config1(built_lib):
+    sys.path.insert(0, ROOT)
+    import bench
+    c = bench.cpu_legs_subprocess()
+    assert c["cores"] >= 1 and c["eval_pdf_all_threads"]["gquery_s"] > 0
+    one, all_ = c["config1_2p20"]["single_thread"], c["config1_2p20"]["all_threads"]
+    assert one["threads"] == 1 and all_["threads"] == c["cores"] and c["config1_2p20"]["pairs"] == 1 << 20
+    for leg in (one, all_):
+        assert leg["eval_pdf_gquery_s"] > 0 and leg["sample_gquery_s"] > 0

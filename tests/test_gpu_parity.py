@@ -140,16 +140,32 @@ def test_context_disables_component(plug):
 
 
 def test_cdf_build(plug, oracle_table):
-    """Device-built row CDFs vs the oracle's own build (same quadrature).  Cell flips at bin
-    edges perturb single quadrature nodes, so the tolerance is on mass, not 1e-5."""
-    got = plug.cdf().cpu().numpy()
-    ref = oracle_table.cdf
+    """Device-built row CDFs vs the oracle's own build (same quadrature, same fp32 node directions).
+    The two differ only by fp32-vs-double cell products, last-ulp sincos differences (a node whose
+    fp32 direction rounds the other way can land in a neighbouring cell: 1/128 of one bin's mass times
+    the cell-to-cell contrast) and the fp32 rounding of the CDF itself (6e-8 per entry).  Bounds:
+    per-bin MASS relative 2e-3 with a 3e-7 absolute floor (two fp32 roundings), CDF entries 5e-5
+    absolute; the count of entries off by more than 1e-5 is recorded (gpurun_out/cdf_build_stats.json)."""
+    import json
+    import os
+    got = plug.cdf().cpu().numpy().astype(np.float64)
+    ref = oracle_table.cdf.astype(np.float64)
     assert got.shape == ref.shape
     assert np.all(got[:, 0] == 0) and np.all(got[:, -1] == 1) and np.all(np.diff(got, axis=1) >= 0)
-    assert np.abs(got - ref).max() < 2e-3
+    d = np.abs(got - ref)
+    pg, pr = np.diff(got, axis=1), np.diff(ref, axis=1)
+    rel = np.abs(pg - pr) / np.maximum(pr, 1e-30)
+    stats = {"entries": int(d.size), "max_abs_cdf_diff": float(d.max()), "entries_off_by_more_than_1e-5": int((d > 1e-5).sum()),
+             "entries_off_by_more_than_1e-6": int((d > 1e-6).sum()), "max_rel_bin_mass_diff": float(rel.max()),
+             "bins_with_rel_mass_diff_over_1e-4": int((rel > 1e-4).sum()), "min_bin_mass": float(pr.min())}
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out_dir):
+        json.dump(stats, open(os.path.join(out_dir, "cdf_build_stats.json"), "w"), indent=1)
+    assert d.max() < 5e-5, stats
+    assert np.all(np.abs(pg - pr) <= 2e-3 * pr + 3e-7), stats
     dens = plug.dens().cpu().numpy()
     from oracle import merl_oracle as O
-    o2 = O.OracleTable(oracle_table.raw, cdf=got)
+    o2 = O.OracleTable(oracle_table.raw, cdf=plug.cdf().cpu().numpy())
     _close(dens, o2.dens, "dens from cdf")
 
 
