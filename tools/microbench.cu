@@ -105,5 +105,15 @@ int main(int argc, char** argv) {
         ms = timeit([&] { stream_red<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], in[5], out[0], out[1], n4); });
         printf("stream+red    grid %4d: %7.3f ms  %7.1f Gq/s  (%6.1f GB/s algorithmic at 36 B/q)\n", grid, ms, n / ms / 1e6, 36.0 * n / ms / 1e6);
     }
+    // stream+gather read 134 / 102 / 134 Gq/s at grids 296 / 592 / 1184.  Sweep the grid in
+    // steps of one CTA per SM (and two off-multiples) with more repetitions, to tell a placement effect from noise.
+    printf("-- grid sweep (20 launches each) --\n");
+    for (int grid : {sms * 1, sms * 2, sms * 3, 444 + 37, sms * 4, sms * 4 + 74, sms * 5, sms * 6, sms * 7, sms * 8, sms * 12, sms * 16}) {
+        float a = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4); }, 20);
+        float b = timeit([&] { copy40<<<grid, 256>>>(in[0], in[1], in[2], in[3], in[4], in[5], out[0], out[1], out[2], out[3], n4); }, 20);
+        float c = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4); }, 20);
+        printf("grid %5d (%5.2f CTA/SM): stream+gather %7.1f / %7.1f Gq/s (two runs)   copy40 %7.1f Gq/s\n", grid, (double)grid / sms,
+               n / a / 1e6, n / c / 1e6, n / b / 1e6);
+    }
     return 0;
 }
