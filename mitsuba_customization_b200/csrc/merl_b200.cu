@@ -231,6 +231,15 @@ __global__ void dens_kernel(const float* __restrict__ cdf, const double* __restr
     dens[k] = (float)(P / (8.0 * 3.14159265358979323846 * (medge[i + 1] - medge[i])));
 }
 
+// guide[j][g] = largest i in [0, nh-1] with cdf[j][i] <= g / kGuideCells (search_guided starts there)
+__global__ void guide_kernel(const float* __restrict__ cdf, int nh, uint8_t* __restrict__ guide) {
+    const float* row = cdf + (size_t)blockIdx.x * (nh + 1);
+    const float u = (float)threadIdx.x / (float)kGuideCells;
+    int i = 0;
+    while (i < nh - 1 && row[i + 1] <= u) ++i;
+    guide[blockIdx.x * kGuideCells + threadIdx.x] = (uint8_t)i;
+}
+
 // ------------------------------------------------------------------------------------------
 // host: launch plumbing
 // ------------------------------------------------------------------------------------------
@@ -359,7 +368,9 @@ static int upload_sampler(merl_table* t, const float* cdf_host, cudaStream_t s) 
     const int nd = d.ni * d.nh;
     dens_kernel<<<(nd + 255) / 256, 256, 0, s>>>(d_cdf, t->d_medge64, d.ni, d.nh, t->d_image + d.off_dens);
     CUDA_TRY(cudaGetLastError());
-    g_launches.fetch_add(1);
+    guide_kernel<<<d.ni, kGuideCells, 0, s>>>(d_cdf, d.nh, reinterpret_cast<uint8_t*>(t->d_image + d.off_guide));
+    CUDA_TRY(cudaGetLastError());
+    g_launches.fetch_add(2);
     return MERL_OK;
 }
 
@@ -406,7 +417,8 @@ static int build_table(const double* planar, const merl_table_params_t* pin, int
     d.off_cdf = d.off_dens + round4(p.ni * p.nh);
     d.off_medge = d.off_cdf + round4(p.ni * (p.nh + 1));
     d.image_eval_floats = d.off_dens + p.ni * p.nh;
-    d.image_full_floats = d.off_medge + p.nh + 1;
+    d.off_guide = d.off_medge + round4(p.nh + 1);
+    d.image_full_floats = d.off_guide + p.ni * kGuideCells / 4;
     if ((size_t)round4(d.image_full_floats) * sizeof(float) > kMaxSmemBytes) {
         const int need = d.image_full_floats;
         delete t;

@@ -33,17 +33,18 @@
 namespace merl {
 
 constexpr int kMaxNH = 256, kMaxND = 256, kMaxNP = 512, kMaxNI = 64;
+constexpr int kGuideCells = 128;   // cells of the sampler's per-row guide table (uint8 bin index each)
 
 // Everything a kernel needs about one table; passed by value as a kernel parameter.
 struct TableDev {
     const float4* cells;     // [nh*nd*np] prescaled RGB (+ validity bits in .w), L2-resident
-    const float* image;      // smem image: thr_h | thr_d | dir_p | dens | cdf | medge  (fp32)
+    const float* image;      // smem image: thr_h | thr_d | dir_p | dens | cdf | medge (fp32) | guide (uint8)
     const double* thr_h64;   // [nh+1] tan^2(theta_i)   (tier 2)
     const double* thr_d64;   // [nd+1] cos^2(theta_k)
     const double2* dir_p64;  // [np+1] (cos, sin)(phi_k)
     int nh, nd, np, ni;
     int theta_h_sqrt;
-    int off_thr_d, off_dir_p, off_dens, off_cdf, off_medge;  // float offsets into image
+    int off_thr_d, off_dir_p, off_dens, off_cdf, off_medge, off_guide;  // float offsets into image
     int image_eval_floats;   // floats needed by eval/pdf/backward kernels (up to dens incl.)
     int image_full_floats;   // floats needed by the sample kernel (everything)
     float kh;                // candidate scale: sqrt map: nh^2*2/pi ; linear: nh*2/pi
@@ -61,6 +62,7 @@ struct SmemView {
     const float* dens;
     const float* cdf;
     const float* medge;
+    const uint8_t* guide;   // [ni][kGuideCells]: largest bin whose CDF entry is <= cell / kGuideCells
 };
 
 __device__ __forceinline__ SmemView make_view(const TableDev& t, const float* smem) {
@@ -71,6 +73,7 @@ __device__ __forceinline__ SmemView make_view(const TableDev& t, const float* sm
     v.dens = smem + t.off_dens;
     v.cdf = smem + t.off_cdf;
     v.medge = smem + t.off_medge;
+    v.guide = reinterpret_cast<const uint8_t*>(smem + t.off_guide);
     return v;
 }
 

@@ -344,6 +344,21 @@ __device__ __forceinline__ int search_lane(const float* row, int nh, int /*step0
     MERL_CHECK(p >= row && p < end);
     return (int)(p - row);
 }
+// Same result with a guide table (MERL_SAMPLE_GUIDE): guide[g] = largest i with row[i] <= g / kGuideCells, so the
+// answer for u in cell g = floor(u kGuideCells) is guide[g] advanced while the next entry is still <= u.  A cell
+// covers 1/kGuideCells of the probability mass whatever its number of bins, so the expected number of forward
+// steps is (nh + kGuideCells) / kGuideCells < 2; cells that span many low-mass tail bins (the cdf_floor mass of
+// high theta_h) take the bisection instead.  Two unrolled steps keep the four queries of a lane interleaved.
+__device__ __forceinline__ int search_guided(const float* row, const uint8_t* guide_row, int nh, float u) {
+    const int g = max(min((int)(u * (float)kGuideCells), kGuideCells - 1), 0);
+    int i = (u == u) ? (int)guide_row[g] : 0;
+    const int last = nh - 1;
+    i += (i < last && row[i + 1] <= u);
+    i += (i < last && row[i + 1] <= u);
+    if (i < last && row[i + 1] <= u) i = search_lane(row, nh, 0, u);   // rare: a long run of low-mass bins
+    MERL_CHECK(i >= 0 && i < nh);
+    return i;
+}
 // Same result, warp-cooperative: the warp walks its queries; for each, every lane tests a
 // strided share of the row (conflict-free LDS) and __ballot_sync/__popc count the entries <= u.
 // row[] is non-decreasing, so that count - 1 is the bisection's answer.
@@ -418,10 +433,18 @@ struct SampleOp {
 #ifndef MERL_PF_SAMPLE
 #define MERL_PF_SAMPLE 1
 #endif
-    static constexpr int kPrefetch = MERL_PF_SAMPLE;
-    static constexpr int kStageVecs = 0;
-    __device__ __forceinline__ void stage(float4*, int64_t) const {}
-    __device__ __forceinline__ unsigned hot_staged(const TableDev&, const SmemView&, int64_t, bool, float4*, int64_t) const { return 0u; }
+#ifndef MERL_SAMPLE_STAGE
+#define MERL_SAMPLE_STAGE 0
+#endif
+#ifndef MERL_SAMPLE_GUIDE
+#define MERL_SAMPLE_GUIDE 0
+#endif
+    // input staging (see cp_async16): the first use of every streamed input was the kernel's top stall
+    // (profiles/r01_sample_ncu_summary.md: long_scoreboard 4.0 of 9 cycles per issue at the first FMUL / FSETP
+    // on loaded data); staged, the inputs of the next group land in the lane's shared-memory slot while the
+    // current group's ~1300 instructions run.  Not with the cooperative search (every lane must reach it).
+    static constexpr int kStageVecs = (MERL_SAMPLE_STAGE && VEC == 4 && !SEARCH) ? 6 : 0;
+    static constexpr int kPrefetch = kStageVecs ? 0 : MERL_PF_SAMPLE;
     SampleIn in;
     SampleOut out;
 
@@ -429,6 +452,23 @@ struct SampleOp {
     __device__ __forceinline__ void prefetch(const int64_t g) const {
         prefetch_stream<VEC>(in.wix, g); prefetch_stream<VEC>(in.wiy, g); prefetch_stream<VEC>(in.wiz, g);
         prefetch_stream<VEC>(in.u1, g); prefetch_stream<VEC>(in.u2x, g); prefetch_stream<VEC>(in.u2y, g);
+    }
+    __device__ __forceinline__ void stage(float4* slot, const int64_t g) const {
+        cp_async16(slot + 0 * kThreadsPerCta, in.wix + 4 * g); cp_async16(slot + 1 * kThreadsPerCta, in.wiy + 4 * g);
+        cp_async16(slot + 2 * kThreadsPerCta, in.wiz + 4 * g); cp_async16(slot + 3 * kThreadsPerCta, in.u1 + 4 * g);
+        cp_async16(slot + 4 * kThreadsPerCta, in.u2x + 4 * g); cp_async16(slot + 5 * kThreadsPerCta, in.u2y + 4 * g);
+    }
+    __device__ __forceinline__ unsigned hot_staged(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                                   float4* slot, const int64_t g_next) const {
+        if (!in_range) return 0u;
+        const Pack<4> ax = load_slot(slot, 0), ay = load_slot(slot, 1), az = load_slot(slot, 2), u1 = load_slot(slot, 3),
+                      ux = load_slot(slot, 4), uy = load_slot(slot, 5);
+        if (g_next >= 0) stage(slot, g_next);
+        cp_async_commit();
+        typedef const Pack<VEC>& R;
+        return body(t, v, g, true, threadIdx.x & 31, load_active<VEC>(in.active, g), reinterpret_cast<R>(ax),
+                    reinterpret_cast<R>(ay), reinterpret_cast<R>(az), reinterpret_cast<R>(u1), reinterpret_cast<R>(ux),
+                    reinterpret_cast<R>(uy));
     }
 
     __device__ __forceinline__ unsigned hot(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
@@ -439,6 +479,12 @@ struct SampleOp {
                         az = load_stream<VEC>(in.wiz, gl), u1 = load_stream<VEC>(in.u1, gl),
                         ux = load_stream<VEC>(in.u2x, gl), uy = load_stream<VEC>(in.u2y, gl);
         const unsigned act = in_range ? load_active<VEC>(in.active, gl) : 0u;
+        return body(t, v, g, in_range, lane, act, ax, ay, az, u1, ux, uy);
+    }
+    __device__ __forceinline__ unsigned body(const TableDev& t, const SmemView& v, const int64_t g, const bool in_range,
+                                             const int lane, const unsigned act, const Pack<VEC>& ax, const Pack<VEC>& ay,
+                                             const Pack<VEC>& az, const Pack<VEC>& u1, const Pack<VEC>& ux,
+                                             const Pack<VEC>& uy) const {
         Pack<VEC> bx, by, bz, pdf, wr, wg, wb;
         uint32_t lobe[VEC];
         int idx[VEC];
@@ -453,7 +499,8 @@ struct SampleOp {
             const int j = max(min((int)(az.v[q] * (float)t.ni), t.ni - 1), 0);
             const float* row = v.cdf + j * (t.nh + 1);
             const int i = SEARCH ? search_warp_coop(v.cdf, t.nh, j, ux.v[q], ok && spec, (unsigned)lane)
-                                 : search_lane(row, t.nh, t.search_step, ux.v[q]);
+                          : MERL_SAMPLE_GUIDE ? search_guided(row, v.guide + j * kGuideCells, t.nh, ux.v[q])
+                                              : search_lane(row, t.nh, t.search_step, ux.v[q]);
             draw_direction(v, row, i, spec, ax.v[q], ay.v[q], az.v[q], ux.v[q], uy.v[q], x, y, z);
             valid[q] = ok && z > 0.f;
             const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], x, y, z);
@@ -725,7 +772,8 @@ struct SampleAosOp {
         float x, y, z;
         const int j = max(min((int)(a.z * (float)t.ni), t.ni - 1), 0);
         const float* row = v.cdf + j * (t.nh + 1);
-        const int i = search_lane(row, t.nh, t.search_step, u.y);
+        const int i = MERL_SAMPLE_GUIDE ? search_guided(row, v.guide + j * kGuideCells, t.nh, u.y)
+                                        : search_lane(row, t.nh, t.search_step, u.y);
         draw_direction(v, row, i, spec, a.x, a.y, a.z, u.y, u.z, x, y, z);
         const bool valid = ok && z > 0.f;
         const HalfDiff h = half_diff_setup(a.x, a.y, a.z, x, y, z);

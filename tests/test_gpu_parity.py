@@ -143,9 +143,11 @@ def test_cdf_build(plug, oracle_table):
     """Device-built row CDFs vs the oracle's own build (same quadrature, same fp32 node directions).
     The two differ only by fp32-vs-double cell products, last-ulp sincos differences (a node whose
     fp32 direction rounds the other way can land in a neighbouring cell: 1/128 of one bin's mass times
-    the cell-to-cell contrast) and the fp32 rounding of the CDF itself (6e-8 per entry).  Bounds:
-    per-bin MASS relative 2e-3 with a 3e-7 absolute floor (two fp32 roundings), CDF entries 5e-5
-    absolute; the count of entries off by more than 1e-5 is recorded (gpurun_out/cdf_build_stats.json)."""
+    the cell-to-cell contrast) and the fp32 rounding of the CDF itself (6e-8 per entry).  Measured on
+    B200 (profiles/r02_cdf_build_stats.json): max |cdf diff| 6.0e-8 = one fp32 ulp, no entry off by more
+    than 1e-6, per-bin mass within 3.9e-6 relative.  Bounds: CDF entries 2.5e-7 absolute, per-bin MASS
+    1e-4 relative with a 2.5e-7 absolute floor (two fp32 roundings); the counts of entries off by more
+    than 1e-5 / 1e-6 are recorded (gpurun_out/cdf_build_stats.json)."""
     import json
     import os
     got = plug.cdf().cpu().numpy().astype(np.float64)
@@ -161,8 +163,8 @@ def test_cdf_build(plug, oracle_table):
     out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
     if os.path.isdir(out_dir):
         json.dump(stats, open(os.path.join(out_dir, "cdf_build_stats.json"), "w"), indent=1)
-    assert d.max() < 5e-5, stats
-    assert np.all(np.abs(pg - pr) <= 2e-3 * pr + 3e-7), stats
+    assert d.max() <= 2.5e-7, stats
+    assert np.all(np.abs(pg - pr) <= 1e-4 * pr + 2.5e-7), stats
     dens = plug.dens().cpu().numpy()
     from oracle import merl_oracle as O
     o2 = O.OracleTable(oracle_table.raw, cdf=plug.cdf().cpu().numpy())

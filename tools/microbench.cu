@@ -66,6 +66,20 @@ __global__ void stream_red(float4* table, const int4* __restrict__ idx, const fl
         red4(table + i.z, x.z + u.z, y.z + v.z, z.z + w.z, p.z + q.z); red4(table + i.w, x.w + u.w, y.w + v.w, z.w + w.w, p.w + q.w);
     }
 }
+__global__ void smid_gather(const float4* __restrict__ table, const int4* __restrict__ idx, const float4* a,
+                            const float4* b, const float4* c, const float4* d, const float4* e, float4* o0,
+                            float4* o1, float4* o2, float4* o3, long n4, int* smid_out) {
+    if (threadIdx.x == 0) { unsigned s; asm("mov.u32 %0, %%smid;" : "=r"(s)); smid_out[blockIdx.x] = (int)s; }
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < n4; g += (long)gridDim.x * blockDim.x) {
+        int4 i = __ldcs(idx + g);
+        float4 x = __ldcs(a + g), y = __ldcs(b + g), z = __ldcs(c + g), u = __ldcs(d + g), v = __ldcs(e + g);
+        float4 p = __ldg(table + i.x), q = __ldg(table + i.y), r = __ldg(table + i.z), s = __ldg(table + i.w);
+        __stcs(o0 + g, make_float4(p.x * x.x, q.x * x.y, r.x * x.z, s.x * x.w));
+        __stcs(o1 + g, make_float4(p.y * y.x, q.y * y.y, r.y * y.z, s.y * y.w));
+        __stcs(o2 + g, make_float4(p.z * z.x, q.z * z.y, r.z * z.z, s.z * z.w));
+        __stcs(o3 + g, make_float4(u.x + v.x, u.y + v.y, u.z + v.z, u.w + v.w));
+    }
+}
 template <typename F> float timeit(F f, int iters = 10) {
     for (int i = 0; i < 3; ++i) f();
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -114,6 +128,41 @@ int main(int argc, char** argv) {
         float c = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4); }, 20);
         printf("grid %5d (%5.2f CTA/SM): stream+gather %7.1f / %7.1f Gq/s (two runs)   copy40 %7.1f Gq/s\n", grid, (double)grid / sms,
                n / a / 1e6, n / c / 1e6, n / b / 1e6);
+    }
+    // Where do the CTAs of each grid land?  (placement imbalance vs. a memory-system effect)
+    printf("-- CTAs per SM (histogram: count x SMs) and the effect of breaking the 2^28-byte stream alignment --\n");
+    int* d_smid; CK(cudaMalloc(&d_smid, 4096 * 4));
+    for (int grid : {sms * 2, sms * 3, 444 + 37, sms * 4, sms * 5, sms * 6, sms * 7, sms * 8}) {
+        CK(cudaMemset(d_smid, 0xff, 4096 * 4));
+        smid_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4, d_smid);
+        CK(cudaDeviceSynchronize());
+        std::vector<int> h(grid); CK(cudaMemcpy(h.data(), d_smid, grid * 4, cudaMemcpyDeviceToHost));
+        std::vector<int> per(256, 0); for (int v : h) if (v >= 0 && v < 256) per[v]++;
+        int hist[17] = {0}; for (int sm = 0; sm < 256; ++sm) if (per[sm] > 0 || sm < sms) hist[per[sm] > 16 ? 16 : per[sm]]++;
+        printf("grid %5d:", grid); for (int c = 0; c <= 16; ++c) if (hist[c]) printf("  %dx%d", c, hist[c]); printf("\n");
+    }
+    // same pattern, every stream shifted by a different odd multiple of 4 KB + 256 B (arrays allocated with slack)
+    {
+        float4 *pin[6], *pout[4];
+        const long slack = 1 << 20;
+        for (int k = 0; k < 6; ++k) { CK(cudaMalloc(&pin[k], n * 4 + slack)); CK(cudaMemset(pin[k], 0, n * 4 + slack)); }
+        for (int k = 0; k < 4; ++k) CK(cudaMalloc(&pout[k], n * 4 + slack));
+        auto sh = [&](float4* p, int k) { return (float4*)((char*)p + (long)(2 * k + 1) * 4352); };
+        for (int grid : {sms * 2, sms * 3, sms * 4, sms * 5, sms * 6, sms * 8}) {
+            float a = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, sh(pin[0], 0), sh(pin[1], 1), sh(pin[2], 2), sh(pin[3], 3), sh(pin[4], 4),
+                                                               sh(pout[0], 5), sh(pout[1], 6), sh(pout[2], 7), sh(pout[3], 8), n4); }, 20);
+            float b = timeit([&] { copy40<<<grid, 256>>>(sh(pin[0], 0), sh(pin[1], 1), sh(pin[2], 2), sh(pin[3], 3), sh(pin[4], 4), sh(pin[5], 9),
+                                                         sh(pout[0], 5), sh(pout[1], 6), sh(pout[2], 7), sh(pout[3], 8), n4); }, 20);
+            printf("shifted streams grid %5d: stream+gather %7.1f Gq/s   copy40 %7.1f Gq/s\n", grid, n / a / 1e6, n / b / 1e6);
+        }
+    }
+    // 200-launch hold of the no-math pattern at the kernel's own grid: does the PATTERN alone hit the power cap?
+    {
+        const int grid = sms * 3;
+        for (int w = 0; w < 6; ++w) {
+            float a = timeit([&] { stream_gather<<<grid, 256>>>(table, idx, in[0], in[1], in[2], in[3], in[4], out[0], out[1], out[2], out[3], n4); }, 200);
+            printf("hold stream+gather grid %d, window %d (200 launches): %7.1f Gq/s\n", grid, w, n / a / 1e6);
+        }
     }
     return 0;
 }
