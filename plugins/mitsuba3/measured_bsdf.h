@@ -9,9 +9,18 @@
 // shading frame, eval includes cos(theta_o), zero unless wi.z > 0 and wo.z > 0, one component
 // (GlossyReflection | FrontSide), errors by Throw().
 //
-// Variants: cuda_* -> device pointers straight through.  scalar_* -> the *_host entry points
-// with n = 1 (correct, PCIe-latency bound; for parity runs).  llvm_* -> the *_host entry points
-// on the packet's host memory.  There is no CPU implementation in this plugin.
+// Variants: cuda_* -> device pointers straight through.  llvm_* -> the whole packet through the
+// *_host entry points (host pointers of the evaluated arrays, n = packet width; the library stages the
+// copies in chunks over three streams), inactive lanes zeroed with dr::select afterwards.  scalar_* ->
+// the *_host entry points with n = 1: correct, but ONE PCIe round trip per query (~1e4-1e5 queries/s);
+// for parity runs only -- the plugin logs that once.  There is no CPU implementation in this plugin.
+//
+// JIT variants need WAVEFRONT mode.  These virtuals call an external kernel, so their arguments must
+// be evaluated arrays (dr::eval + .data()).  Under Dr.Jit's default flags Mitsuba records virtual
+// function calls and loops symbolically: the arguments are placeholders then and evaluating one
+// raises deep inside Dr.Jit.  The plugin checks for that first and says what to do:
+//     dr.set_flag(dr.JitFlag.VCallRecord, False); dr.set_flag(dr.JitFlag.LoopRecord, False)   # Dr.Jit 0.4
+//     dr.set_flag(dr.JitFlag.SymbolicCalls, False); dr.set_flag(dr.JitFlag.SymbolicLoops, False)   # 1.x
 #pragma once
 #include <mitsuba/core/fresolver.h>
 #include <mitsuba/core/properties.h>
@@ -22,6 +31,14 @@
 #include <algorithm>
 
 #include "../common/merl_host.h"
+
+// "Dr.Jit is recording symbolically right now": JitFlag::Recording in drjit-core 0.4.x, renamed
+// SymbolicScope in 1.x (both: set only while a call / loop is being captured).
+#if defined(DRJIT_VERSION_MAJOR) && DRJIT_VERSION_MAJOR >= 1
+#  define MERL_JIT_RECORDING_FLAG JitFlag::SymbolicScope
+#else
+#  define MERL_JIT_RECORDING_FLAG JitFlag::Recording
+#endif
 
 NAMESPACE_BEGIN(mitsuba)
 
@@ -57,6 +74,7 @@ public:
         MI_MASKED_FUNCTION(ProfilerPhase::BSDFEvaluate, active_);
         if (!ctx.is_enabled(BSDFFlags::GlossyReflection)) return Spectrum(0.f);
         if constexpr (dr::is_cuda_v<Float>) {
+            require_wavefront();
             // *_ad_* variants: when `data` carries gradients the evaluation enters the AD graph as
             // one custom operation whose adjoint is the scatter kernel (merl_eval_op.h)
             if constexpr (dr::is_diff_v<Float>) {
@@ -72,6 +90,7 @@ public:
     // The kernel call itself, on detached operands (cuda variants only).
     Spectrum eval_primal(const Vector3f& wi_, const Vector3f& wo_, Mask active_) const {
         if constexpr (dr::is_cuda_v<Float>) {
+            require_wavefront();
             Vector3f wi = wi_, wo = wo_;
             Mask active = active_;
             const size_t n = materialise(wi, wo, active);
@@ -91,6 +110,7 @@ public:
         MI_MASKED_FUNCTION(ProfilerPhase::BSDFEvaluate, active_);
         if (!ctx.is_enabled(BSDFFlags::GlossyReflection)) return Float(0.f);
         if constexpr (dr::is_cuda_v<Float>) {
+            require_wavefront();
             Vector3f wi = si.wi, wo = wo_;
             Mask active = active_;
             const size_t n = materialise(wi, wo, active);
@@ -110,6 +130,7 @@ public:
         MI_MASKED_FUNCTION(ProfilerPhase::BSDFEvaluate, active_);
         if (!ctx.is_enabled(BSDFFlags::GlossyReflection)) return { Spectrum(0.f), Float(0.f) };
         if constexpr (dr::is_cuda_v<Float>) {
+            require_wavefront();
             Vector3f wi = si.wi, wo = wo_;
             Mask active = active_;
             const size_t n = materialise(wi, wo, active);
@@ -135,7 +156,8 @@ public:
             bs.sampled_type = UInt32(0u); bs.sampled_component = UInt32(0u);
             return { bs, Spectrum(0.f) };
         }
-        if constexpr (dr::is_cuda_v<Float>) {
+        if constexpr (dr::is_jit_v<Float>) {
+            require_wavefront();
             Vector3f wi = si.wi;
             Float u1 = sample1_;
             Point2f u2 = sample2_;
@@ -148,11 +170,25 @@ public:
                   p = dr::empty<Float>(n), wr = dr::empty<Float>(n), wg = dr::empty<Float>(n),
                   wb = dr::empty<Float>(n);
             UInt32 lobe = dr::empty<UInt32>(n);
-            check(merl_sample(m_table.get(), wi.x().data(), wi.y().data(), wi.z().data(), u1.data(),
-                              u2.x().data(), u2.y().data(), mask_ptr(active), (int64_t) n, ox.data(), oy.data(),
-                              oz.data(), p.data(), wr.data(), wg.data(), wb.data(), lobe.data(),
-                              jit_cuda_stream()),
-                  "sample");
+            if constexpr (dr::is_cuda_v<Float>) {
+                check(merl_sample(m_table.get(), wi.x().data(), wi.y().data(), wi.z().data(), u1.data(),
+                                  u2.x().data(), u2.y().data(), mask_ptr(active), (int64_t) n, ox.data(), oy.data(),
+                                  oz.data(), p.data(), wr.data(), wg.data(), wb.data(), lobe.data(),
+                                  jit_cuda_stream()),
+                      "sample");
+            } else {
+                // llvm_*: the packet's host memory through the host-buffer entry point, all n lanes in one
+                // call; lanes that were masked out are zeroed afterwards (the entry point takes no mask)
+                check(merl_sample_host(m_table.get(), wi.x().data(), wi.y().data(), wi.z().data(), u1.data(),
+                                       u2.x().data(), u2.y().data(), (int64_t) n, ox.data(), oy.data(), oz.data(),
+                                       p.data(), wr.data(), wg.data(), wb.data(), lobe.data()),
+                      "sample");
+                const Float zero(0.f);
+                ox = dr::select(active, ox, zero); oy = dr::select(active, oy, zero); oz = dr::select(active, oz, zero);
+                p = dr::select(active, p, zero);
+                wr = dr::select(active, wr, zero); wg = dr::select(active, wg, zero); wb = dr::select(active, wb, zero);
+                lobe = dr::select(active, lobe, UInt32(0u));
+            }
             bs.wo = Vector3f(ox, oy, oz);
             bs.pdf = p;
             bs.eta = Float(1.f);
@@ -161,6 +197,7 @@ public:
             m_last_lobe = lobe;
             return { bs, Spectrum(wr, wg, wb) };
         } else {
+            warn_scalar_once();
             const float wi[3] = { (float) si.wi.x(), (float) si.wi.y(), (float) si.wi.z() };
             const float u[3] = { (float) sample1_, (float) sample2_.x(), (float) sample2_.y() };
             float o[3] = {}, p = 0.f, w[3] = {};
@@ -212,12 +249,13 @@ public:
 
     // grad_cells4: device float4[ncell] (zeroed by the caller) += d eval / d data . grad_out.
     void backward_table(const SurfaceInteraction3f& si, const Vector3f& wo_, const Spectrum& grad_out_,
-                        Mask active_, float* grad_cells4, bool warp_aggregate = true) const {
+                        Mask active_, float* grad_cells4, bool warp_aggregate = false) const {
         backward_table(si.wi, wo_, grad_out_, active_, grad_cells4, warp_aggregate);
     }
     void backward_table(const Vector3f& wi_, const Vector3f& wo_, const Spectrum& grad_out_, Mask active_,
-                        float* grad_cells4, bool warp_aggregate = true) const {
+                        float* grad_cells4, bool warp_aggregate = false) const {
         if constexpr (dr::is_cuda_v<Float>) {
+            require_wavefront();
             Vector3f wi = wi_, wo = wo_;
             Spectrum go = grad_out_;
             Mask active = active_;
@@ -272,8 +310,42 @@ protected:
     // Dr.Jit CUDA masks store one byte per lane, which is what the ABI's `active` expects.
     static const uint8_t* mask_ptr(const Mask& m) { return reinterpret_cast<const uint8_t*>(m.data()); }
 
-    // scalar_* variants: one query through the host-buffer entry point.
+    // JIT variants: refuse to run inside a symbolic recording (see the header comment).
+    void require_wavefront() const {
+        if constexpr (dr::is_jit_v<Float>) {
+            if (jit_flag(MERL_JIT_RECORDING_FLAG))
+                Throw("%s: this BSDF calls an external CUDA kernel and needs evaluated arrays, but Dr.Jit is recording "
+                      "this call symbolically.  Render in wavefront mode: switch off JitFlag::VCallRecord and "
+                      "JitFlag::LoopRecord (Dr.Jit 1.x: SymbolicCalls and SymbolicLoops) before rendering.", m_plugin);
+        }
+    }
+    // scalar_* variants pay one PCIe round trip per query: say so once per process.
+    void warn_scalar_once() const {
+        static bool warned = false;
+        if (!warned) {
+            warned = true;
+            Log(Warn, "%s: scalar variant -- every eval/pdf/sample call is one host->GPU->host round trip "
+                      "(~1e4-1e5 queries/s).  Use a cuda_* variant (device arrays, ~1e11 queries/s) or an llvm_* "
+                      "variant (whole packets per call); scalar variants are for parity checks.", m_plugin);
+        }
+    }
+
+    // non-CUDA variants.  llvm_*: the whole packet in one call of the host-buffer entry point;
+    // scalar_*: one query.
     std::pair<Spectrum, Float> eval_pdf_packet(const Vector3f& wi_, const Vector3f& wo_, Mask active) const {
+        if constexpr (dr::is_llvm_v<Float>) {
+            require_wavefront();
+            Vector3f wi = wi_, wo = wo_;
+            const size_t n = materialise(wi, wo, active);
+            Float r = dr::empty<Float>(n), g = dr::empty<Float>(n), b = dr::empty<Float>(n), p = dr::empty<Float>(n);
+            check(merl_eval_pdf_host(m_table.get(), wi.x().data(), wi.y().data(), wi.z().data(), wo.x().data(),
+                                     wo.y().data(), wo.z().data(), (int64_t) n, r.data(), g.data(), b.data(), p.data()),
+                  "eval_pdf");
+            const Float zero(0.f);
+            return { Spectrum(dr::select(active, r, zero), dr::select(active, g, zero), dr::select(active, b, zero)),
+                     dr::select(active, p, zero) };
+        } else {
+        warn_scalar_once();
         const float wi[3] = { (float) wi_.x(), (float) wi_.y(), (float) wi_.z() };
         const float wo[3] = { (float) wo_.x(), (float) wo_.y(), (float) wo_.z() };
         float c[3] = {}, p = 0.f;
@@ -282,6 +354,7 @@ protected:
                                      &c[1], &c[2], &p),
                   "eval_pdf");
         return { Spectrum(c[0], c[1], c[2]), Float(p) };
+        }
     }
 
     const char* m_plugin;

@@ -50,6 +50,19 @@ NAMESPACE_BEGIN(mitsuba)
     throw std::runtime_error(buf);
 }
 
+// upstream: Log(LogLevel, fmt, ...) routes through the thread's Logger; the mock keeps the lines
+enum LogLevel { Trace, Debug, Info, Warn, Error };
+inline std::vector<std::string>& mock_log() { static std::vector<std::string> l; return l; }
+inline void Log(LogLevel level, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    mock_log().push_back(std::string(level == Warn ? "[WARN] " : "[LOG] ") + buf);
+    std::fprintf(stderr, "%s\n", mock_log().back().c_str());
+}
+
 template <typename T> class ref {                                   // intrusive in upstream; plain here
 public:
     ref(T* p = nullptr) : m_p(p) {}
