@@ -1213,9 +1213,11 @@ extern "C" int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count,
 typedef void (*XchgKernel)(const PeerView, const int64_t, const float4*, uint32_t*, int*);
 static XchgKernel xchg_kernel_for(int nranks) {
     switch (nranks) {
-        case 1: return peer_allreduce_kernel<1, 2>;   // nothing to sum; the mask pass still runs
-        case 2: return peer_allreduce_kernel<2, 2>;
-        case 4: return peer_allreduce_kernel<4, 2>;
+        // ranks x unroll = 16 loads of 16 B in flight per thread (a remote load takes ~3 us under load; on 2
+        // GPUs unroll 2 left the kernel latency-bound: 67 us for 23.3 MB, profiles/r02_v2_bench_n2.json)
+        case 1: return peer_allreduce_kernel<1, 4>;   // nothing to sum; the mask pass still runs
+        case 2: return peer_allreduce_kernel<2, 8>;
+        case 4: return peer_allreduce_kernel<4, 4>;
         case 8: return peer_allreduce_kernel<8, 2>;
         default: return peer_allreduce_kernel<0, 1>;
     }

@@ -78,6 +78,7 @@ public:
         float u1, u2x;
         splitSample(sample_.x, u1, u2x);
         const float u2y = sample_.y;
+        warnScalarOnce();
         float o[3], w[3];
         uint32_t lobe;
         check(merl_sample_host(m_table.get(), &bRec.wi.x, &bRec.wi.y, &bRec.wi.z, &u1, &u2x, &u2y, 1, &o[0], &o[1],
@@ -136,11 +137,23 @@ protected:
     bool enabled(const BSDFSamplingRecord& bRec) const {
         return (bRec.typeMask & EGlossyReflection) && (bRec.component == -1 || bRec.component == 0);
     }
+    // The scalar virtuals are one host->GPU->host round trip per query (no CPU implementation exists in this
+    // plugin): correct, and ~1e4-1e5 queries/s.  Said once per process; the batched path is WavefrontStage.
+    void warnScalarOnce() const {
+        static bool warned = false;
+        if (!warned) {
+            warned = true;
+            Log(EWarn, "%s: BSDF::eval/pdf/sample run ONE PCIe round trip per call on this plugin (no CPU path); "
+                       "an integrator that gathers a bounce's hits should use WavefrontStage (wavefront_stage.h), "
+                       "which serves whole batches at ~1e11 queries/s.", m_plugin);
+        }
+    }
     size_t cellCount() const { return (size_t) m_params.nh * (size_t) m_params.nd * (size_t) m_params.np; }
 
     bool evalPdfOne(const BSDFSamplingRecord& bRec, EMeasure measure, Spectrum& value, Float& pdf) const {
         if (measure != ESolidAngle || !enabled(bRec) || Frame::cosTheta(bRec.wi) <= 0 || Frame::cosTheta(bRec.wo) <= 0)
             return false;
+        warnScalarOnce();
         float c[3];
         check(merl_eval_pdf_host(m_table.get(), &bRec.wi.x, &bRec.wi.y, &bRec.wi.z, &bRec.wo.x, &bRec.wo.y,
                                  &bRec.wo.z, 1, &c[0], &c[1], &c[2], &pdf), "eval");

@@ -76,6 +76,71 @@ int main(int argc, char** argv) {
             write_vec(fo, out);
             write_vec(fo, lobe);
         }
+        {   // ---- llvm_rgb-like variant: whole packet in host memory, one call per virtual --------
+            using FloatL = dr::LLVMArray<float>;
+            using SpectrumL = Vector<FloatL, 3>;
+            auto bsdf = make<FloatL, SpectrumL>(kind, props);
+            SurfaceInteraction<FloatL, SpectrumL> si;
+            Vector<FloatL, 3> wod;
+            for (int c = 0; c < 3; ++c) {
+                si.wi.v[c] = dr::load<FloatL>(wi.data() + c * n, n);
+                wod.v[c] = dr::load<FloatL>(wo.data() + c * n, n);
+            }
+            auto active = dr::load<dr::LLVMArray<bool>>(act.data(), n);
+            const int64_t calls0 = merl_launch_count();
+            auto [rgb, pdf] = bsdf->eval_pdf(ctx, si, wod, active);
+            auto rgb_only = bsdf->eval(ctx, si, wod, active);
+            auto pdf_only = bsdf->pdf(ctx, si, wod, active);
+            Vector<FloatL, 2> s2(dr::load<FloatL>(u2.data(), n), dr::load<FloatL>(u2.data() + n, n));
+            auto [bs, weight] = bsdf->sample(ctx, si, dr::load<FloatL>(u1.data(), n), s2, active);
+            std::ofstream fl(std::string(argv[4]) + ".llvm", std::ios::binary);
+            auto host = [](const FloatL& a) { std::vector<float> h(a.size()); dr::store(h.data(), a); return h; };
+            for (int c = 0; c < 3; ++c) write_vec(fl, host(rgb.v[c]));
+            write_vec(fl, host(pdf));
+            for (int c = 0; c < 3; ++c) write_vec(fl, host(rgb_only.v[c]));
+            write_vec(fl, host(pdf_only));
+            for (int c = 0; c < 3; ++c) write_vec(fl, host(bs.wo.v[c]));
+            write_vec(fl, host(bs.pdf));
+            for (int c = 0; c < 3; ++c) write_vec(fl, host(weight.v[c]));
+            std::vector<uint32_t> lobe(n);
+            dr::store(lobe.data(), static_cast<MeasuredBSDF<FloatL, SpectrumL>*>(bsdf.get())->last_sampled_lobe());
+            write_vec(fl, lobe);
+            std::cout << "llvm variant: " << n << " lanes per call, " << (merl_launch_count() - calls0)
+                      << " library launches for 4 virtuals" << std::endl;
+            // JIT variants refuse to run inside a symbolic recording, with a message that says what to do
+            jit_set_flag(JitFlag::Recording, 1);
+            bool refused = false;
+            try { bsdf->eval(ctx, si, wod, active); } catch (const std::exception& e) {
+                refused = std::string(e.what()).find("wavefront") != std::string::npos;
+            }
+            jit_set_flag(JitFlag::Recording, 0);
+            if (!refused) Throw("the llvm variant did not refuse a symbolic recording");
+        }
+        {   // the same guard on the cuda variant (before any data() / eval() can raise inside Dr.Jit)
+            auto bsdf = make<FloatC, SpectrumC>(kind, props);
+            SurfaceInteraction<FloatC, SpectrumC> si;
+            Vector<FloatC, 3> wod;
+            for (int c = 0; c < 3; ++c) { si.wi.v[c] = dr::load<FloatC>(wi.data() + c * n, n); wod.v[c] = dr::load<FloatC>(wo.data() + c * n, n); }
+            jit_set_flag(JitFlag::Recording, 1);
+            int refused = 0;
+            auto expect = [&](auto&& call) {
+                try { call(); } catch (const std::exception& e) {
+                    refused += std::string(e.what()).find("wavefront") != std::string::npos;
+                }
+            };
+            expect([&] { bsdf->eval(ctx, si, wod, true); });
+            expect([&] { bsdf->pdf(ctx, si, wod, true); });
+            expect([&] { bsdf->eval_pdf(ctx, si, wod, true); });
+            expect([&] { bsdf->sample(ctx, si, FloatC(0.5f), Vector<FloatC, 2>(FloatC(0.5f), FloatC(0.5f)), true); });
+            jit_set_flag(JitFlag::Recording, 0);
+            if (refused != 4) Throw("the cuda variant refused %d of 4 virtuals inside a recording", refused);
+            std::cout << "recording guard ok" << std::endl;
+        }
+        {
+            size_t warns = 0;
+            for (const auto& l : mock_log()) warns += l.find("[WARN]") == 0 && l.find("scalar variant") != std::string::npos;
+            std::cout << "scalar warning lines: " << warns << std::endl;
+        }
         std::cout << "m3_host_test ok: " << n << " queries, " << merl_launch_count() << " kernel launches" << std::endl;
         return 0;
     } catch (const std::exception& e) {

@@ -86,6 +86,14 @@ def test_mitsuba3_host_marshals_every_argument(cpu_binaries, tmp_path):
     np.testing.assert_allclose(blk[11], np.where(on, wi[0] + 2 * wi[1] + 4 * wi[2], 0), rtol=1e-6)
     assert np.array_equal(blk[12], np.where(on, 2 * u1, 0)) and np.array_equal(blk[14], np.where(on, 2 * u2[1], 0))
     assert np.array_equal(blk[15].view(np.uint32), np.where(on, np.arange(n) & 1, 0).astype(np.uint32))
+    # llvm variant: the WHOLE packet per virtual through the *_host entry points (one library call each,
+    # not one per lane), masked lanes zeroed afterwards -> the same position codes as the cuda block
+    lb = np.fromfile(o + ".llvm", dtype=np.float32).reshape(16, n)
+    assert np.array_equal(lb, blk)
+    assert f"llvm variant: {n} lanes per call, 4 library launches for 4 virtuals" in r.stdout
+    # JIT variants refuse a symbolic recording with a message naming wavefront mode; scalar variants warn ONCE
+    assert "recording guard ok" in r.stdout and "scalar warning lines: 1" in r.stdout
+    assert r.stderr.count("[WARN]") == 1 and "round trip" in r.stderr
     # scalar variant: one query per call -> always cell 0, lobe 0; inactive lanes stay zero
     m = 64
     sc = raw[16 * n:16 * n + 15 * m].reshape(15, m)
@@ -132,6 +140,8 @@ def test_mitsuba06_host_marshals_every_argument(cpu_binaries, tmp_path):
     r = subprocess.run([cpu_binaries["m06_host_test"], "customized_measurment", tab, str(tmp_path / "q.bin"), o,
                         "thetaHRes=6", "thetaDRes=5", "phiDRes=8"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
+    # the scalar virtuals say ONCE that they are one PCIe round trip per call and name the batched path
+    assert r.stderr.count("round trip") == 1 and "WavefrontStage" in r.stderr
     raw = np.fromfile(o, dtype=np.float32)
     ep = raw[:4 * n].reshape(n, 4).T
     on = active.astype(bool)

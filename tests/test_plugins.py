@@ -153,6 +153,10 @@ def test_mitsuba3_plugin_matches_oracle(binaries, kind, tmp_path):
     # the C++ host and the ctypes host drive the same kernels: identical bits
     for got, want in zip((rgb, pdf, s_wo, s_pdf, s_w, lobe), _python_path(plug, wi, wo, u1, u2, active)):
         assert np.array_equal(got, want)
+    # llvm variant: whole packets through the *_host entry points -> the same bits as the cuda variant
+    lb = np.fromfile(o + ".llvm", dtype=np.float32).reshape(16, n)
+    assert np.array_equal(lb, blk)
+    assert "recording guard ok" in r.stdout and "scalar warning lines: 1" in r.stdout
     # scalar variant: first 64 queries one by one through the *_host entry points
     m = 64
     sc = raw[16 * n:16 * n + 15 * m].reshape(15, m)
