@@ -302,8 +302,13 @@ template <typename Op, int MINB>
 static int launch_op(const merl_table* t, const Op& op, int image_floats, int64_t ngroups, cudaStream_t s) {
     const int img = (int)(((size_t)image_floats * sizeof(float) + 127) & ~(size_t)127);
     const size_t stage = (size_t)Op::kStageVecs * 16 * kThreads;
-    return launch_persistent(t, stream_kernel<Op, MINB>, (size_t)img + kQueueBytes + stage, ngroups, s, t->dev, op, ngroups,
-                             img);
+    return launch_persistent(t, stream_kernel<Op, MINB>, (size_t)img + kQueueBytes + stage + op_extra_smem<Op>::value, ngroups, s,
+                             t->dev, op, ngroups, img);
+}
+// byte offset of an op's CTA scratch (Op::kExtraSmem) in the kernel's dynamic shared memory
+template <typename Op> static int extra_smem_offset(int image_floats) {
+    const int img = (int)(((size_t)image_floats * sizeof(float) + 127) & ~(size_t)127);
+    return img + kQueueBytes + Op::kStageVecs * 16 * kThreads;
 }
 static inline int eval_floats(const merl_table* t, bool pdf) { return pdf ? t->dev.image_eval_floats : t->dev.off_dens; }
 
@@ -869,7 +874,7 @@ struct BackwardIn {
     const float *gr, *gg, *gb;
 };
 
-template <int AGG, int GATHER>
+template <int AGG, int GATHER, int CTA = 0>
 static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* grad, cudaStream_t s, bool mask_pass) {
     const int fl = t->dev.off_dens;
     const QueryIn& q = in.q;
@@ -878,16 +883,16 @@ static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* g
                      aligned(in.gg, 16) && aligned(in.gb, 16);
     int64_t done = 0;
     if (vec && n >= 4) {
-        using Op = BackwardOp<4, AGG, GATHER>;
-        const int rc = launch_op<Op, MERL_BWD_MINB>(t, Op{in.q, in.gr, in.gg, in.gb, grad}, fl, n / 4, s);
+        using Op = BackwardOp<4, AGG, GATHER, CTA>;
+        const int rc = launch_op<Op, MERL_BWD_MINB>(t, Op{in.q, in.gr, in.gg, in.gb, grad, extra_smem_offset<Op>(fl)}, fl, n / 4, s);
         if (rc) return rc;
         done = (n / 4) * 4;
     }
     if (done < n) {
-        using Op = BackwardOp<1, AGG, GATHER>;
+        using Op = BackwardOp<1, AGG, GATHER, 0>;
         in.q = offset_in(in.q, done);
         in.gr += done; in.gg += done; in.gb += done;
-        const int rc = launch_op<Op, 3 * kMinbScale>(t, Op{in.q, in.gr, in.gg, in.gb, grad}, fl, n - done, s);
+        const int rc = launch_op<Op, 3 * kMinbScale>(t, Op{in.q, in.gr, in.gg, in.gb, grad, 0}, fl, n - done, s);
         if (rc) return rc;
     }
     if (!GATHER && n > 0 && mask_pass) {
@@ -918,6 +923,8 @@ extern "C" int merl_backward(const merl_table_t* t, const float* wix, const floa
     const bool defer = (flags & MERL_BWD_DEFER_MASK) != 0;
     if (defer && t->params.clamp_negative) gather = false;
     const bool mp = !defer;
+    // coherent batches: lane fold + warp fold + CTA-wide shared-memory accumulator, blocked work assignment
+    if (flags & MERL_BWD_CTA_AGGREGATE) return gather ? run_backward<1, 1, 1>(t, in, n, grad, s, mp) : run_backward<1, 0, 1>(t, in, n, grad, s, mp);
     if (flags & MERL_BWD_WARP_AGGREGATE) return gather ? run_backward<1, 1>(t, in, n, grad, s, mp) : run_backward<1, 0>(t, in, n, grad, s, mp);
     return gather ? run_backward<0, 1>(t, in, n, grad, s, mp) : run_backward<0, 0>(t, in, n, grad, s, mp);
 }
@@ -1756,8 +1763,13 @@ static int merl_render_impl(const merl_table_t* const* tables, int ntables, cons
         // depth 0: camera rays and their first intersection in one kernel over the whole pass; its
         // hits form the depth-0 live list.  Every other kernel walks a live list (grid-stride over
         // a grid that covers a few waves; CTAs beyond the live count exit at once).
-        rt_primary_kernel<<<nb, 256, sizeof(int) * ntables, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_live[0], d_nlive, d_counts);
         const int g = std::min(nb, t0->num_sms * 16);
+#ifndef MERL_PRIMARY_PERSISTENT
+#define MERL_PRIMARY_PERSISTENT 1
+#endif
+        // the camera-ray kernel on the same few-waves grid as the others: the scene is staged and the
+        // per-material histogram flushed once per CTA, i.e. ~14x less often than with one CTA per 256 paths
+        rt_primary_kernel<<<MERL_PRIMARY_PERSISTENT ? g : nb, 256, sizeof(int) * ntables, q>>>(R, P, A, d_sph, d_clus, d_smat, d_pass, film, d_live[0], d_nlive, d_counts);
         for (int depth = 0; depth <= p->max_depth; ++depth) {
             const int cur = depth & 1, nxt = cur ^ 1;
             const LiveList L{d_live[cur], d_nlive + cur, d_live[nxt], d_nlive + nxt};

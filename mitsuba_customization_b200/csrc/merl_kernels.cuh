@@ -13,6 +13,8 @@
 #include "merl_device.cuh"
 #include "merl_slow.cuh"
 
+#include <type_traits>
+
 namespace merl {
 
 // ------------------------------------------------------------------------------------------
@@ -131,6 +133,16 @@ __device__ __forceinline__ void flush_queue(const Op& op, const TableDev& t, con
 //                                   warp, so ops may use warp collectives); returns bit q set
 //                                   when query g*kVec+q must be re-done
 //   void redo(t, v, i)              exact pass over the single query i
+// Optional members of an Op, detected here so that the other ops stay as they are:
+//   static constexpr bool kBlocked   true: every CTA walks ONE contiguous range of groups instead of a grid
+//                                    stride (coherent batches: what a CTA sees stays local in cell space)
+//   static constexpr int kExtraSmem  bytes of CTA-shared scratch after the queues and staging slots;
+//                                    void cta_begin(char*) / cta_end(char*) run by all threads around the loop
+template <typename Op, typename = void> struct op_blocked : std::false_type {};
+template <typename Op> struct op_blocked<Op, std::void_t<decltype(Op::kBlocked)>> : std::bool_constant<Op::kBlocked> {};
+template <typename Op, typename = void> struct op_extra_smem : std::integral_constant<int, 0> {};
+template <typename Op> struct op_extra_smem<Op, std::void_t<decltype(Op::kExtraSmem)>> : std::integral_constant<int, Op::kExtraSmem> {};
+
 template <typename Op, int MINB>
 __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const TableDev t, const Op op,
                                                                       const int64_t ngroups, const int image_bytes) {
@@ -139,29 +151,45 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const WarpQueue wq = warp_queue(reinterpret_cast<char*>(smem4) + image_bytes, warp);
     if (lane == 0) *wq.count = 0;
+    constexpr bool kBlk = op_blocked<Op>::value;
+    constexpr int kExtra = op_extra_smem<Op>::value;
+    char* const extra = reinterpret_cast<char*>(smem4) + image_bytes + kQueueBytes + Op::kStageVecs * 16 * kThreadsPerCta;
+    if constexpr (kExtra > 0) op.cta_begin(extra);
     stage_image(t, smem, op.image_floats(t));   // ends with __syncthreads()
     const SmemView v = make_view(t, smem);
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // grid stride: group g of iteration k is blockIdx * blockDim + k * gridDim * blockDim + thread;
+    // blocked: CTA b owns groups [b * per_cta, (b + 1) * per_cta), per_cta a multiple of blockDim
+    int64_t first, last, stride;
+    if constexpr (kBlk) {
+        const int64_t per_cta = ((ngroups + gridDim.x - 1) / gridDim.x + kThreadsPerCta - 1) / kThreadsPerCta * kThreadsPerCta;
+        first = min((int64_t)blockIdx.x * per_cta, ngroups);
+        last = min(first + per_cta, ngroups);
+        stride = kThreadsPerCta;
+    } else {
+        first = blockIdx.x * (int64_t)blockDim.x;
+        last = ngroups;
+        stride = (int64_t)gridDim.x * blockDim.x;
+    }
     // this lane's staging slot: vector k of the group at slot[k * blockDim] (conflict-free)
     float4* const slot = reinterpret_cast<float4*>(reinterpret_cast<char*>(smem4) + image_bytes + kQueueBytes) + threadIdx.x;
     if (Op::kStageVecs > 0) {
-        const int64_t gf = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-        if (gf < ngroups) op.stage(slot, gf);
+        const int64_t gf = first + threadIdx.x;
+        if (gf < last) op.stage(slot, gf);
         cp_async_commit();
     }
     // warp-uniform trip count: flush and some ops use warp-level synchronisation
-    for (int64_t g0 = blockIdx.x * (int64_t)blockDim.x + (threadIdx.x & ~31); g0 < ngroups; g0 += stride) {
+    for (int64_t g0 = first + (threadIdx.x & ~31); g0 < last; g0 += stride) {
         const int64_t g = g0 + lane;
         if (Op::kPrefetch > 0) {
             const int64_t gp = g + stride * Op::kPrefetch;
-            if (gp < ngroups) op.prefetch(gp);
+            if (gp < last) op.prefetch(gp);
         }
         unsigned m;
         if (Op::kStageVecs > 0) {
             cp_async_wait_all();
-            m = op.hot_staged(t, v, g, g < ngroups, slot, g + stride < ngroups ? g + stride : (int64_t)-1);
+            m = op.hot_staged(t, v, g, g < last, slot, g + stride < last ? g + stride : (int64_t)-1);
         } else {
-            m = op.hot(t, v, g, g < ngroups, lane);
+            m = op.hot(t, v, g, g < last, lane);
         }
         if (m) {
 #pragma unroll
@@ -176,6 +204,7 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
         if (*reinterpret_cast<volatile int*>(wq.count) > kQueueCap - 32 * Op::kVec) flush_queue(op, t, v, wq, lane);
     }
     flush_queue(op, t, v, wq, lane);
+    if constexpr (kExtra > 0) op.cta_end(extra);
 }
 
 // pdf of the two-lobe sampler given the theta_h bin (row A5; oracle: eval_pdf_one).  Branch-free:
@@ -567,9 +596,55 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
 // its own contribution.  GATHER = 0: contributions are added unmasked and backward_mask_kernel
 // zeroes the channels of invalid cells afterwards in one pass over the table (47 MB of traffic,
 // cheaper than the per-query gather once the batch has more queries than the table has cells).
-template <int VEC, int AGG, int GATHER>
+// CTA = 1 (MERL_BWD_CTA_AGGREGATE, coherent batches): blocked work assignment, and after the lane- and warp-level
+// folds the contribution goes into a CTA-wide direct-mapped table in shared memory (kCtaHashSlots cells: key =
+// cell index, value = float4 sum) instead of straight to L2; a slot held by another cell sends the contribution
+// to L2 as before.  The table is flushed once, when the CTA has walked its range: one vector RED per distinct
+// resident cell.  Shared-memory float atomics are CAS loops on sm_100a (ATOMS.CAST.SPIN), so this only pays
+// when the folds before it have removed the intra-warp conflicts and the batch revisits cells.
+constexpr int kCtaHashSlots = 2048;
+constexpr int kCtaHashBytes = kCtaHashSlots * (4 + 16);
+
+template <int VEC, int AGG, int GATHER, int CTA = 0>
 struct BackwardOp {
     static constexpr int kVec = VEC;
+    static constexpr bool kBlocked = CTA != 0;
+    static constexpr int kExtraSmem = CTA ? kCtaHashBytes : 0;
+    __device__ __forceinline__ int* hash_keys() const {
+        extern __shared__ float4 smem4[];
+        return reinterpret_cast<int*>(reinterpret_cast<char*>(smem4) + extra_off);
+    }
+    __device__ __forceinline__ float* hash_vals() const { return reinterpret_cast<float*>(hash_keys() + kCtaHashSlots); }
+    __device__ __forceinline__ void cta_begin(char* extra) const {
+        int* keys = reinterpret_cast<int*>(extra);
+        float4* vals = reinterpret_cast<float4*>(keys + kCtaHashSlots);
+        for (int i = threadIdx.x; i < kCtaHashSlots; i += blockDim.x) { keys[i] = -1; vals[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
+        // (stage_image's barrier, which follows, orders this before the first use)
+    }
+    __device__ __forceinline__ void cta_end(char* extra) const {
+        __syncthreads();
+        const int* keys = reinterpret_cast<const int*>(extra);
+        const float4* vals = reinterpret_cast<const float4*>(keys + kCtaHashSlots);
+        for (int i = threadIdx.x; i < kCtaHashSlots; i += blockDim.x) {
+            const int key = keys[i];
+            if (key >= 0) { const float4 a = vals[i]; red_add_v4(grad + key, a.x, a.y, a.z, a.w); }
+        }
+    }
+    // contribution of one (already folded) query group: CTA table first, L2 when its slot belongs to another cell
+    __device__ __forceinline__ void emit(const int idx, const float v0, const float v1, const float v2, const float v3) const {
+        if (CTA) {
+            int* keys = hash_keys();
+            const unsigned slot = ((unsigned)idx * 2654435761u) >> (32 - 11);
+            static_assert(kCtaHashSlots == 2048, "slot = top 11 bits of the hash");
+            const int old = atomicCAS(&keys[slot], -1, idx);
+            if (old == -1 || old == idx) {
+                float* a = hash_vals() + 4 * slot;
+                atomicAdd(a, v0); atomicAdd(a + 1, v1); atomicAdd(a + 2, v2); atomicAdd(a + 3, v3);
+                return;
+            }
+        }
+        red_add_v4(grad + idx, v0, v1, v2, v3);
+    }
 #ifndef MERL_PF_BACKWARD
 #define MERL_PF_BACKWARD 0
 #endif
@@ -582,6 +657,7 @@ struct BackwardOp {
     QueryIn q;
     const float *gr, *gg, *gb;
     float4* grad;
+    int extra_off;   // byte offset of the CTA table in dynamic shared memory (set by the host launcher)
 
     __device__ __forceinline__ int image_floats(const TableDev& t) const { return t.off_dens; }
     __device__ __forceinline__ void prefetch(const int64_t g) const {
@@ -630,7 +706,7 @@ struct BackwardOp {
                                              const Pack<VEC>& bz, const Pack<VEC>& cr, const Pack<VEC>& cg,
                                              const Pack<VEC>& cb) const {
         int idx[VEC];
-        bool emit[VEC];
+        bool live[VEC];
         unsigned uncmask = 0;
 #pragma unroll
         for (int k = 0; k < VEC; ++k) {
@@ -640,20 +716,39 @@ struct BackwardOp {
             int kc[3];
             const Bins b = compute_bins_fast(t, v, ax.v[k], ay.v[k], az.v[k], bx.v[k], by.v[k], bz.v[k], h, unc, kc);
             uncmask |= (unsigned)((unc != 0u) & valid) << k;
-            emit[k] = valid & (unc == 0u);   // an uncertain query adds nothing here: redo() does its RED
+            live[k] = valid & (unc == 0u);   // an uncertain query adds nothing here: redo() does its RED
             idx[k] = flat_index(t, b);
         }
         float bits[VEC];
 #pragma unroll
         for (int k = 0; k < VEC; ++k)
             bits[k] = GATHER ? __ldg(&reinterpret_cast<const float*>(t.cells)[4 * (int64_t)idx[k] + 3]) : 7.f;
+        float a0[VEC], a1[VEC], a2[VEC], a3[VEC];
 #pragma unroll
         for (int k = 0; k < VEC; ++k) {
             const int m = (int)bits[k];
-            const float c = emit[k] ? bz.v[k] : 0.f;
-            float v0 = (m & 1) ? cr.v[k] * c : 0.f, v1 = (m & 2) ? cg.v[k] * c : 0.f,
-                  v2 = (m & 4) ? cb.v[k] * c : 0.f, v3 = emit[k] ? 1.f : 0.f;
-            bool em = emit[k];
+            const float c = live[k] ? bz.v[k] : 0.f;
+            a0[k] = (m & 1) ? cr.v[k] * c : 0.f; a1[k] = (m & 2) ? cg.v[k] * c : 0.f;
+            a2[k] = (m & 4) ? cb.v[k] * c : 0.f; a3[k] = live[k] ? 1.f : 0.f;
+        }
+        if (AGG && VEC > 1) {
+            // a lane's own consecutive queries first (registers only): query k folds into the first earlier
+            // query of the lane with the same cell
+#pragma unroll
+            for (int k = VEC - 1; k > 0; --k) {
+#pragma unroll
+                for (int j = 0; j < k; ++j) {
+                    if (live[k] && live[j] && idx[k] == idx[j]) {
+                        a0[j] += a0[k]; a1[j] += a1[k]; a2[j] += a2[k]; a3[j] += a3[k];
+                        live[k] = false;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            float v0 = a0[k], v1 = a1[k], v2 = a2[k], v3 = a3[k];
+            bool em = live[k];
             if (AGG) {
                 // lanes of this warp that hit the same cell fold into the lowest such lane
                 const int key = em ? idx[k] : -1 - lane;
@@ -680,7 +775,7 @@ struct BackwardOp {
                     }
                 }
             }
-            if (em) red_add_v4(grad + idx[k], v0, v1, v2, v3);
+            if (em) this->emit(idx[k], v0, v1, v2, v3);
         }
         return in_range ? uncmask : 0u;
     }

@@ -33,6 +33,10 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 __device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+// a fifth uniform from the low bytes of three words (the bits u01 discards)
+__device__ __forceinline__ float u01_low(uint32_t a, uint32_t b, uint32_t c) {
+    return (float)(((a & 0xffu) << 16) | ((b & 0xffu) << 8) | (c & 0xffu)) * (1.0f / 16777216.0f);
+}
 
 struct Camera {
     float px, py, pz;     // position
@@ -289,9 +293,11 @@ __device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P
         return false;
     }
     if (!PRIMARY) smp = P.sample[i];
-    uint32_t re[4], rb[4];
-    philox4x32_10((uint32_t)pixel, (uint32_t)smp, (uint32_t)(2 * depth + 1), 0u, R.k0, R.k1, re);
-    philox4x32_10((uint32_t)pixel, (uint32_t)smp, (uint32_t)(2 * depth + 2), 0u, R.k0, R.k1, rb);
+    // ONE Philox call per surface interaction: four 24-bit uniforms from the high bits of its words (emitter
+    // direction, lobe choice, first BSDF number) and a fifth from the low bytes u01() does not use
+    uint32_t re[4];
+    philox4x32_10((uint32_t)pixel, (uint32_t)smp, (uint32_t)(depth + 1), 0u, R.k0, R.k1, re);
+    const float u5 = u01_low(re[0], re[1], re[2]);
     // emitter sampling: uniform direction on the sphere (constant environment), pdf 1/(4 pi)
     const float ez = 1.f - 2.f * u01(re[0]);
     const float er = sqrtf(fmaxf(0.f, 1.f - ez * ez));
@@ -318,7 +324,7 @@ __device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P
     P.mat[i] = m;
     S.wi4[i] = make_float4(wix, wiy, wiz, (float)m);
     S.woe4[i] = woe;
-    S.u4[i] = make_float4(u01(rb[0]), u01(rb[1]), u01(rb[2]), 0.f);
+    S.u4[i] = make_float4(u01(re[2]), u01(re[3]), u5, 0.f);
     return true;
 }
 
@@ -400,27 +406,42 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
 __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int ntables, int* seg_off, int* cursor,
                                                        int* item_off, const int target_items, int* next_live_count,
                                                        unsigned long long* __restrict__ nquery) {
-    __shared__ int sc[1024];
+    __shared__ int warp_tot[32];
     __shared__ int chunk_s;
-    const int k = threadIdx.x;
+    const int k = threadIdx.x, lane = k & 31, warp = k >> 5;
     if (k == 0) *next_live_count = 0;   // this bounce's shade kernel appends the continuing paths
     const int c = k < ntables ? counts[k] : 0;
-    auto scan = [&](int v) {
-        sc[k] = v;
-        __syncthreads();
-        for (int o = 1; o < 1024; o <<= 1) {
-            const int add = k >= o ? sc[k - o] : 0;
-            __syncthreads();
-            sc[k] += add;
-            __syncthreads();
+    // inclusive scan over the 1024 threads: shuffles inside a warp, the 32 warp totals scanned by warp 0
+    // (two barriers per scan; the Hillis-Steele form it replaces took twenty)
+    auto scan = [&](int v, int& total) {
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += u;
         }
-        return sc[k];
+        if (lane == 31) warp_tot[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_tot[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += u;
+            }
+            warp_tot[lane] = w;
+        }
+        __syncthreads();
+        total = warp_tot[31];
+        const int r = v + (warp ? warp_tot[warp - 1] : 0);
+        __syncthreads();   // warp_tot is reused by the next scan
+        return r;
     };
-    const int inc = scan(c);
+    int total;
+    const int inc = scan(c, total);
     if (k < ntables) { seg_off[k] = inc - c; cursor[k] = inc - c; counts[k] = 0; }
-    if (k == 1023) {
-        *nquery += (unsigned long long)sc[1023];   // statistics: BSDF queries of the whole render
-        int ch = (sc[1023] + target_items - 1) / max(target_items, 1);
+    if (k == 0) {
+        *nquery += (unsigned long long)total;   // statistics: BSDF queries of the whole render
+        int ch = (total + target_items - 1) / max(target_items, 1);
         ch = (ch + 31) & ~31;
         chunk_s = min(max(ch, 128), 8192);
     }
@@ -428,8 +449,8 @@ __global__ void __launch_bounds__(1024) rt_scan_kernel(int* counts, const int nt
     __syncthreads();
     const int chunk = chunk_s;
     const int items = (c + chunk - 1) / chunk;
-    __syncthreads();
-    const int iinc = scan(items);
+    int itotal;
+    const int iinc = scan(items, itotal);
     if (k < ntables) item_off[k] = iinc - items;
     if (k == ntables - 1) { item_off[ntables] = iinc; item_off[ntables + 1] = chunk; }
 }

@@ -115,9 +115,12 @@ void orc_render(const orc_table_t *tables, int ntables, const double *spheres, c
                 const double wi[3] = {(float)-dot3(d, fs), (float)-dot3(d, ft), (float)-dot3(d, n)};
                 if (!(wi[2] > 0.0)) break;
                 const orc_table_t *tb = tables + sphere_mat[hit];
-                uint32_t re[4], rb[4];
-                philox4x32_10((uint32_t)pixel, (uint32_t)s, (uint32_t)(2 * depth + 1), 0u, k0, k1, re);
-                philox4x32_10((uint32_t)pixel, (uint32_t)s, (uint32_t)(2 * depth + 2), 0u, k0, k1, rb);
+                /* one Philox call per surface interaction: four uniforms from the high 24 bits of its words
+                 * (emitter direction, lobe choice, first BSDF number), a fifth from their unused low bytes */
+                uint32_t re[4];
+                philox4x32_10((uint32_t)pixel, (uint32_t)s, (uint32_t)(depth + 1), 0u, k0, k1, re);
+                const float u5 = (float)(((re[0] & 0xffu) << 16) | ((re[1] & 0xffu) << 8) | (re[2] & 0xffu)) *
+                                 (1.0f / 16777216.0f);
                 /* emitter sampling: uniform direction, pdf 1/(4 pi) */
                 const double ez = 1.0 - 2.0 * u01(re[0]), er = sqrt(fmax(0.0, 1.0 - ez * ez));
                 const double ephi = 2.0 * M_PI * u01(re[1]);
@@ -133,7 +136,7 @@ void orc_render(const orc_table_t *tables, int ntables, const double *spheres, c
                 }
                 /* BSDF sampling */
                 double wo[3];
-                draw_direction(tb, wi, u01(rb[0]), u01(rb[1]), u01(rb[2]), wo);
+                draw_direction(tb, wi, u01(re[2]), u01(re[3]), u5, wo);
                 const double wof[3] = {(float)wo[0], (float)wo[1], (float)wo[2]};
                 double fb[3], pdf;
                 eval_pdf_one(tb, wi, wof, fb, &pdf, NULL);

@@ -92,7 +92,7 @@ def test_forward_properties_at_full_size(plug, orc, logn):
     _close(pdf[sel].cpu().numpy()[stable], ref_pdf[stable], "pdf")
 
 
-@pytest.mark.parametrize("agg", [True, False])
+@pytest.mark.parametrize("agg", [{"warp_aggregate": True}, {}, {"cta_aggregate": True}])
 def test_backward_is_adjoint_at_full_size(plug, agg):
     """BASELINE config 4: 2^26 queries scattered into one fp32 gradient table."""
     n = 1 << 26
@@ -100,7 +100,7 @@ def test_backward_is_adjoint_at_full_size(plug, agg):
     wi, wo = _hemi(n, gen), _hemi(n, gen)
     g = torch.rand(3, n, device="cuda", generator=gen)         # same sign: the fp32 sums stay well conditioned
     ctx, si = _ctx_si(wi)
-    grad = plug.backward(si, wo, g, warp_aggregate=agg)
+    grad = plug.backward(si, wo, g, **agg)
     counts = grad[:, 3]
     assert float(counts.double().sum()) == float(n)             # every query is valid here
     assert torch.equal(counts, counts.round())

@@ -250,21 +250,26 @@ def test_sample_chi2(plug):
     assert abs(hist.sum() / n - cell.sum()) < 5e-3  # mass that stays above the horizon
 
 
-@pytest.mark.parametrize("agg", [True, False])
+def _agg(mode):
+    """plain per-lane RED / lane + warp fold / lane + warp fold + CTA shared-memory accumulator (blocked ranges)"""
+    return {"plain": {}, "warp": {"warp_aggregate": True}, "cta": {"cta_aggregate": True}}[mode]
+
+
+@pytest.mark.parametrize("agg", ["plain", "warp", "cta"])
 def test_backward_parity(plug, orc, agg):
     from mitsuba_customization_b200 import synth
     n = (1 << 20) + 2
     wi, wo = synth.random_queries(n, seed=77)
     rng = np.random.default_rng(5)
     g = np.abs(rng.standard_normal((3, n))).astype(np.float32)  # same-sign: fp32 sums stay well-conditioned
-    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), warp_aggregate=agg)
+    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), **_agg(agg))
     ref = orc.backward(wi, wo, g)
     _close(grad[:, :3].cpu().numpy(), ref[:, :3], "grad")
     valid = (wi[2] > 0) & (wo[2] > 0)
     assert float(grad[:, 3].sum()) == float(valid.sum())
 
 
-@pytest.mark.parametrize("agg", [True, False])
+@pytest.mark.parametrize("agg", ["plain", "warp", "cta"])
 @pytest.mark.parametrize("n", [1 << 18, (1 << 21) + 3])
 def test_backward_masks_invalid_channels(raw_table, agg, n):
     """A table with invalid (negative) channels scattered through it: those channels get no gradient,
@@ -280,7 +285,7 @@ def test_backward_masks_invalid_channels(raw_table, agg, n):
     assert n < plug.info.ncell or n > plug.info.ncell
     wi, wo = synth.random_queries(n, seed=n)
     g = np.abs(np.random.default_rng(3).standard_normal((3, n))).astype(np.float32)
-    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), warp_aggregate=agg)
+    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), **_agg(agg))
     ref = orc.backward(wi, wo, g)
     got = grad.cpu().numpy()
     _close(got[:, :3], ref[:, :3], "grad with invalid channels")
@@ -291,12 +296,20 @@ def test_backward_masks_invalid_channels(raw_table, agg, n):
     for c in range(3):
         assert np.all(got[(dead >> c) & 1 == 0, c] == 0.0)
     # accumulating a second batch into the same buffer keeps the invariant
-    plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), grad_cells=grad, warp_aggregate=agg)
+    plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), grad_cells=grad, **_agg(agg))
     _close(grad.cpu().numpy()[:, :3], 2 * ref[:, :3], "accumulated grad")
+    # deferred mask: scatter unmasked (whatever the batch size), mask applied once afterwards
+    g2 = torch.zeros_like(grad)
+    plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), grad_cells=g2, defer_mask=True, **_agg(agg))
+    plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), grad_cells=g2, defer_mask=True, **_agg(agg))
+    plug.apply_grad_mask(g2)
+    _close(g2.cpu().numpy()[:, :3], 2 * ref[:, :3], "deferred-mask grad")
+    assert np.array_equal(g2.cpu().numpy()[:, 3], 2 * counts)
 
 
-def test_backward_coherent_batch(plug, orc):
-    """Many queries per cell (a coherent wavefront): exercises the warp-aggregation paths.
+@pytest.mark.parametrize("agg", ["warp", "cta", "plain"])
+def test_backward_coherent_batch(plug, orc, agg):
+    """Many queries per cell (a coherent wavefront): exercises the lane / warp / CTA aggregation paths.
     An fp32 gradient table (BASELINE.json) accumulates `count` terms per cell with rounding
     error <= count * 2^-24 * sum|terms|, so beyond ~170 hits per cell that bound, not 1e-5,
     is the achievable tolerance; the test applies whichever is larger."""
@@ -308,7 +321,7 @@ def test_backward_coherent_batch(plug, orc):
     wi[:, 5::7] = wi8[:, [3]]  # break up some warps into mixed groups
     wo[:, 5::7] = wo8[:, [3]]
     g = np.full((3, wi.shape[1]), 2.0 ** -8, dtype=np.float32)
-    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda()).cpu().numpy()
+    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), **_agg(agg)).cpu().numpy()
     ref = orc.backward(wi, wo, g)
     count = grad[:, 3:4].astype(np.float64)
     assert count.sum() == wi.shape[1]
@@ -317,7 +330,7 @@ def test_backward_coherent_batch(plug, orc):
     # small groups (<= 32 hits, one warp's worth) meet the plain 1e-5 bar
     wi, wo = np.ascontiguousarray(np.repeat(wi8, 32, axis=1)), np.ascontiguousarray(np.repeat(wo8, 32, axis=1))
     g = np.random.default_rng(1).random((3, wi.shape[1])).astype(np.float32)
-    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda())
+    grad = plug.backward(_si(wi), torch.from_numpy(wo).cuda(), torch.from_numpy(g).cuda(), **_agg(agg))
     _close(grad[:, :3].cpu().numpy(), orc.backward(wi, wo, g)[:, :3], "grad (32 per cell)")
 
 
