@@ -596,54 +596,71 @@ __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float
 // its own contribution.  GATHER = 0: contributions are added unmasked and backward_mask_kernel
 // zeroes the channels of invalid cells afterwards in one pass over the table (47 MB of traffic,
 // cheaper than the per-query gather once the batch has more queries than the table has cells).
-// CTA = 1 (MERL_BWD_CTA_AGGREGATE, coherent batches): blocked work assignment, and after the lane- and warp-level
-// folds the contribution goes into a CTA-wide direct-mapped table in shared memory (kCtaHashSlots cells: key =
-// cell index, value = float4 sum) instead of straight to L2; a slot held by another cell sends the contribution
-// to L2 as before.  The table is flushed once, when the CTA has walked its range: one vector RED per distinct
-// resident cell.  Shared-memory float atomics are CAS loops on sm_100a (ATOMS.CAST.SPIN), so this only pays
-// when the folds before it have removed the intra-warp conflicts and the batch revisits cells.
-constexpr int kCtaHashSlots = 2048;
-constexpr int kCtaHashBytes = kCtaHashSlots * (4 + 16);
+// CTA = 1 (MERL_BWD_CTA_AGGREGATE, coherent batches): blocked work assignment (a CTA walks one contiguous range
+// of the batch, so what it sees stays local in cell space), and after the lane- and warp-level folds the
+// contribution goes into the warp's PRIVATE accumulator table in shared memory (kWarpTableSlots cells, direct
+// mapped: key = cell index, value = float4 sum) instead of straight to L2.  A warp owns its table, and after the
+// warp fold the contributing lanes hold distinct cells, so the table needs no atomics: lanes that map to the
+// same slot in one step are told apart with one more __match_any_sync (the lowest takes the slot, the others
+// go to L2), and a slot that holds another cell is EVICTED (its sum goes to L2 with one vector RED) and taken
+// over, which keeps the table on the cells the warp is currently visiting.  Flushed when the warp is done.
+// (A first version used one CTA-wide table with shared-memory float atomics: those are CAS loops on sm_100a
+// -- ATOMS.CAST.SPIN -- and it lost 15-30 % on every workload, profiles/r02_coherent_bwd.txt.)
+constexpr int kWarpTableSlots = 128;
+constexpr int kWarpTableLog2 = 7;
+constexpr int kCtaTableBytes = kWarpsPerCta * kWarpTableSlots * (4 + 16);
 
 template <int VEC, int AGG, int GATHER, int CTA = 0>
 struct BackwardOp {
     static constexpr int kVec = VEC;
     static constexpr bool kBlocked = CTA != 0;
-    static constexpr int kExtraSmem = CTA ? kCtaHashBytes : 0;
-    __device__ __forceinline__ int* hash_keys() const {
+    static constexpr int kExtraSmem = CTA ? kCtaTableBytes : 0;
+    static_assert(!CTA || AGG, "the warp tables need the warp fold (distinct cells per step)");
+    __device__ __forceinline__ int* warp_keys() const {
         extern __shared__ float4 smem4[];
-        return reinterpret_cast<int*>(reinterpret_cast<char*>(smem4) + extra_off);
+        return reinterpret_cast<int*>(reinterpret_cast<char*>(smem4) + extra_off) + (threadIdx.x >> 5) * kWarpTableSlots;
     }
-    __device__ __forceinline__ float* hash_vals() const { return reinterpret_cast<float*>(hash_keys() + kCtaHashSlots); }
+    __device__ __forceinline__ float4* warp_vals() const {
+        extern __shared__ float4 smem4[];
+        return reinterpret_cast<float4*>(reinterpret_cast<char*>(smem4) + extra_off + kWarpsPerCta * kWarpTableSlots * 4) +
+               (threadIdx.x >> 5) * kWarpTableSlots;
+    }
     __device__ __forceinline__ void cta_begin(char* extra) const {
         int* keys = reinterpret_cast<int*>(extra);
-        float4* vals = reinterpret_cast<float4*>(keys + kCtaHashSlots);
-        for (int i = threadIdx.x; i < kCtaHashSlots; i += blockDim.x) { keys[i] = -1; vals[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
+        for (int i = threadIdx.x; i < kWarpsPerCta * kWarpTableSlots; i += blockDim.x) keys[i] = -1;
         // (stage_image's barrier, which follows, orders this before the first use)
     }
-    __device__ __forceinline__ void cta_end(char* extra) const {
-        __syncthreads();
-        const int* keys = reinterpret_cast<const int*>(extra);
-        const float4* vals = reinterpret_cast<const float4*>(keys + kCtaHashSlots);
-        for (int i = threadIdx.x; i < kCtaHashSlots; i += blockDim.x) {
+    __device__ __forceinline__ void cta_end(char*) const {
+        __syncwarp();
+        const int* keys = warp_keys();
+        const float4* vals = warp_vals();
+        for (int i = threadIdx.x & 31; i < kWarpTableSlots; i += 32) {
             const int key = keys[i];
             if (key >= 0) { const float4 a = vals[i]; red_add_v4(grad + key, a.x, a.y, a.z, a.w); }
         }
     }
-    // contribution of one (already folded) query group: CTA table first, L2 when its slot belongs to another cell
-    __device__ __forceinline__ void emit(const int idx, const float v0, const float v1, const float v2, const float v3) const {
-        if (CTA) {
-            int* keys = hash_keys();
-            const unsigned slot = ((unsigned)idx * 2654435761u) >> (32 - 11);
-            static_assert(kCtaHashSlots == 2048, "slot = top 11 bits of the hash");
-            const int old = atomicCAS(&keys[slot], -1, idx);
-            if (old == -1 || old == idx) {
-                float* a = hash_vals() + 4 * slot;
-                atomicAdd(a, v0); atomicAdd(a + 1, v1); atomicAdd(a + 2, v2); atomicAdd(a + 3, v3);
-                return;
+    // One step of the warp (all 32 lanes call it): lanes with `em` hold DISTINCT cells.
+    __device__ __forceinline__ void table_add(const bool em, const int idx, const float v0, const float v1, const float v2,
+                                              const float v3, const int lane) const {
+        const unsigned slot = ((unsigned)idx * 2654435761u) >> (32 - kWarpTableLog2);
+        const unsigned peers = __match_any_sync(0xffffffffu, em ? (int)slot : -1 - lane);
+        const bool win = em && lane == __ffs(peers) - 1;
+        if (em && !win) red_add_v4(grad + idx, v0, v1, v2, v3);      // another cell of this step took the slot
+        if (win) {
+            int* keys = warp_keys();
+            float4* vals = warp_vals();
+            const int key = keys[slot];
+            float4 a = vals[slot];
+            if (key == idx) {
+                a.x += v0; a.y += v1; a.z += v2; a.w += v3;
+            } else {
+                if (key >= 0) red_add_v4(grad + key, a.x, a.y, a.z, a.w);   // evict
+                keys[slot] = idx;
+                a = make_float4(v0, v1, v2, v3);
             }
+            vals[slot] = a;
         }
-        red_add_v4(grad + idx, v0, v1, v2, v3);
+        __syncwarp();
     }
 #ifndef MERL_PF_BACKWARD
 #define MERL_PF_BACKWARD 0
@@ -775,7 +792,8 @@ struct BackwardOp {
                     }
                 }
             }
-            if (em) this->emit(idx[k], v0, v1, v2, v3);
+            if (CTA) table_add(em, idx[k], v0, v1, v2, v3, lane);
+            else if (em) red_add_v4(grad + idx[k], v0, v1, v2, v3);
         }
         return in_range ? uncmask : 0u;
     }

@@ -16,6 +16,20 @@ def _relmse(a, b):
     return float(((a - b) ** 2).mean() / (b ** 2).mean())
 
 
+def _relmse_trimmed(a, b, frac=1e-3):
+    """relMSE with the worst `frac` of the pixels left out.  The harness traces in fp32 and the oracle in double:
+    a ray that grazes a silhouette, or a wi within an ulp of a bin edge, takes another branch in a handful of
+    pixels per seed (tools/render_diff.py: 1-20 of 6144 pixels differ by more than 1e-3 at every seed, the rest
+    agree to < 1e-3), and on a 96x64x8-spp image ONE such path with a large f/pdf weight moves the plain relMSE by
+    1e-4.  At BASELINE's sizes the same flips are diluted to 1e-8..1e-7 (the full-size tests below use the plain
+    metric); the small scenes bound the plain metric loosely and the trimmed one tightly."""
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    e = ((a - b) ** 2).sum(axis=-1).ravel()
+    k = int(np.ceil(frac * e.size))
+    e = np.sort(e)[:e.size - k]
+    return float(e.sum() / a.shape[-1] / e.size / (b ** 2).mean())
+
+
 @pytest.fixture(scope="module")
 def pair(raw_table):
     from mitsuba_customization_b200 import bsdf
@@ -83,7 +97,8 @@ def test_multi_material_grid_matches_oracle():
     got = film.cpu().numpy()
     np.testing.assert_allclose(got[..., 3], 1.0, atol=1e-5)
     assert st["bsdf_queries"] > st["paths"] * 0.2          # inter-reflections happen
-    assert _relmse(got[..., :3], ref[..., :3]) <= REL_MSE
+    assert _relmse(got[..., :3], ref[..., :3]) <= 10 * REL_MSE
+    assert _relmse_trimmed(got[..., :3], ref[..., :3]) <= REL_MSE / 10
 
 
 def test_render_argument_errors(pair):
