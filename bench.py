@@ -337,7 +337,29 @@ def run_b200(args):
         e2e_s = float(t.item())
     e2e_value = world * n * e2e_steps / e2e_s / 1e9
     checksum = float(hout[3, :: max(1, n // 4096)].double().sum())
-    del hwi, hwo, hout
+    # what the host link alone allows: the same bytes (24 B/query up, 16 B/query down) as plain pinned copies on two
+    # streams, no kernel -- if e2e sits at this figure the path is bound by PCIe / host memory, not by the library
+    s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+    d_in, d_out = torch.empty(6, n, device=dev), torch.empty(4, n, device=dev)
+    h_in = torch.empty(6, n).pin_memory()
+
+    def copies():
+        with torch.cuda.stream(s_up):
+            d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(s_dn):
+            hout.copy_(d_out, non_blocking=True)
+    copies(); torch.cuda.synchronize(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(4):
+        copies()
+    torch.cuda.synchronize()
+    cp_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([cp_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        cp_s = float(t.item())
+    e2e_copy_ceiling = world * n * 4 / cp_s / 1e9
+    del hwi, hwo, hout, h_in, d_in, d_out
 
     # ---- other kernels of the path (reported, not the headline) --------------------------
     extras = {}
@@ -440,7 +462,10 @@ def run_b200(args):
             "clocks": sampler.summary(),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 16 * n,
                     "steps": e2e_steps, "call": "MERL.eval_pdf_host -> merl_eval_pdf_host (pinned host buffers)",
-                    "result_checksum": checksum},
+                    "result_checksum": checksum,
+                    "host_link_ceiling": {"value": e2e_copy_ceiling, "unit": UNIT,
+                                          "what": "the same 24 B/query up + 16 B/query down as plain pinned cudaMemcpyAsync on "
+                                                  "two streams per rank, all ranks at once, no kernel"}},
             "gpu_launches": int(launches),
             "roofline": roof,
             "extras": extras,

@@ -56,7 +56,12 @@ wo_dir = to_local(L)
 def hemi(k):
     z = torch.rand(k, device=dev, generator=gen).clamp_min(1e-6); p = torch.rand(k, device=dev, generator=gen) * 2 * math.pi
     r = torch.sqrt(1 - z * z); return torch.stack([r * torch.cos(p), r * torch.sin(p), z]).contiguous()
-sets = {"render (wo random per path)": (wi, wo_render), "directional light": (wi, wo_dir), "random pairs": (hemi(m), hemi(m))}
+# extreme reuse: a flat surface seen from far away under a distant light -- every query in one of a handful of cells
+flat_wi = torch.tensor([0.3, 0.1, 0.95], device=dev); flat_wi = (flat_wi / flat_wi.norm())[:, None].expand(3, m).contiguous()
+flat_wo = torch.tensor([-0.2, 0.4, 0.89], device=dev); flat_wo = (flat_wo / flat_wo.norm())[:, None].expand(3, m)
+flat_wo = (flat_wo + 2e-3 * torch.randn(3, m, device=dev, generator=gen)); flat_wo = (flat_wo / flat_wo.norm(dim=0)).contiguous()
+sets = {"render (wo random per path)": (wi, wo_render), "directional light": (wi, wo_dir), "random pairs": (hemi(m), hemi(m)),
+        "flat surface, distant light": (flat_wi, flat_wo)}
 g = torch.rand(3, m, device=dev, generator=gen)
 modes = {"plain": {}, "warp": {"warp_aggregate": True}, "cta": {"cta_aggregate": True}}
 def timeit(fn, it=10):
