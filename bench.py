@@ -511,6 +511,10 @@ def grad_legs(plug, si, wo, n, world, rank, local, comm, timed, gen, k):
 
     transports = {}
     bufs = {"peer": D.PeerBuffer(comm, 4 * ncell, "peer"), "nccl_registered": D.PeerBuffer(comm, 4 * ncell, "nccl")}
+    try:   # the library's own multimem kernel through the switch; every rank gets the same verdict
+        bufs["nvls"] = D.PeerBuffer(comm, 4 * ncell, "nvls")
+    except bsdf.MerlError as e:
+        out["nvls_unavailable"] = str(e)[:160]
     for name, pb in bufs.items():
         gt = pb.tensor((ncell, 4))
         res = {"registration": pb.registration}

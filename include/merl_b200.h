@@ -270,6 +270,12 @@ int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_strea
  *     No host-side state per call: capturable in a CUDA graph.
  *   MERL_XCHG_NCCL: ncclMemAlloc + registration with the communicator (symmetric window, else
  *     ncclCommRegister); merl_peerbuf_allreduce is ncclAllReduce in place (+ the mask pass).
+ *   MERL_XCHG_NVLS: the buffer is an NCCL symmetric window with a multicast mapping (NCCL >= 2.28,
+ *     NVSwitch); merl_peerbuf_allreduce is this library's own kernel: rank r reads slab r with
+ *     multimem.ld_reduce (the switch adds the R copies), applies the mask, writes it back to all R
+ *     copies with multimem.st; multicast flag barriers.  MERL_ERR_UNSUPPORTED when the build had no
+ *     NCCL device headers, the loaded NCCL differs from them, or there is no multicast over all ranks
+ *     (every rank gets the same answer, so a host can fall back to another transport collectively).
  * merl_peerbuf_allreduce(count = floats to sum, multiple of 4; mask_table = NULL or the table whose
  * gradient this is, then count must be 4 * ncell) is asynchronous on `stream`; every rank must call it
  * with the same count, and exchanges of one communicator must be issued in the same order everywhere.
@@ -277,6 +283,7 @@ int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_strea
 typedef struct merl_peerbuf merl_peerbuf_t;
 #define MERL_XCHG_PEER 0
 #define MERL_XCHG_NCCL 1
+#define MERL_XCHG_NVLS 2
 typedef struct merl_peerbuf_info {
     float* data;               /* device float[count], owned by the library */
     int64_t count;

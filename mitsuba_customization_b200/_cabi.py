@@ -31,7 +31,8 @@ SYMBOLS = [
 BWD_WARP_AGGREGATE = 1
 BWD_DEFER_MASK = 2
 BWD_CTA_AGGREGATE = 4
-XCHG_PEER, XCHG_NCCL = 0, 1
+XCHG_PEER, XCHG_NCCL, XCHG_NVLS = 0, 1, 2
+ERR_UNSUPPORTED = -5
 
 
 class MerlError(RuntimeError):

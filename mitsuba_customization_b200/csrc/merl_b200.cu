@@ -21,6 +21,20 @@
 #include <string>
 #include <vector>
 
+// NCCL's device-side API (2.28+): only its host-visible types are used here -- the symmetric window and
+// device communicator are opened on the host and reduced to raw unicast / multicast pointers that
+// merl_exchange.cuh's own kernel takes (transport MERL_XCHG_NVLS).  Optional at build time.
+#if defined(__has_include)
+#if __has_include(<nccl.h>) && __has_include(<nccl_device/impl/comm__types.h>)
+#include <nccl.h>
+#include <nccl_device/impl/comm__types.h>
+#define MERL_HAVE_NCCL_DEVICE 1
+#endif
+#endif
+#ifndef MERL_HAVE_NCCL_DEVICE
+#define MERL_HAVE_NCCL_DEVICE 0
+#endif
+
 #include "../../include/merl_b200.h"
 #include "merl_kernels.cuh"
 #include "merl_render.cuh"
@@ -1125,6 +1139,8 @@ struct NcclApi {
     int (*CommWindowRegister)(void* comm, void* buf, size_t size, void** win, int flags) = nullptr;
     int (*CommWindowDeregister)(void* comm, void* win) = nullptr;
     int (*GetVersion)(int* v) = nullptr;
+    int (*DevCommCreate)(void* comm, const void* requirements, void* dev_comm_out) = nullptr;   // NCCL >= 2.28
+    int (*DevCommDestroy)(void* comm, const void* dev_comm) = nullptr;
     bool ok = false;
 };
 NcclApi* nccl_api() {
@@ -1148,6 +1164,8 @@ NcclApi* nccl_api() {
         *(void**)&api.CommWindowRegister = dlsym(h, "ncclCommWindowRegister");
         *(void**)&api.CommWindowDeregister = dlsym(h, "ncclCommWindowDeregister");
         *(void**)&api.GetVersion = dlsym(h, "ncclGetVersion");
+        *(void**)&api.DevCommCreate = dlsym(h, "ncclDevCommCreate");
+        *(void**)&api.DevCommDestroy = dlsym(h, "ncclDevCommDestroy");
         api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce;
     });
     return &api;
@@ -1161,6 +1179,12 @@ int nccl_fail(const char* what, int rc) {
 struct merl_comm {
     void* comm = nullptr;
     int device = 0, nranks = 1, rank = 0;
+#if MERL_HAVE_NCCL_DEVICE
+    // device communicator with a multicast mapping of the local (NVLink) team, made on first use by an
+    // MERL_XCHG_NVLS buffer (collective: every rank creates its NVLS buffers in the same order)
+    ncclDevComm dev_comm{};
+    int dev_comm_state = 0;   // 0 not tried, 1 ready, -1 unavailable
+#endif
 };
 
 extern "C" int merl_comm_unique_id(void* id_out) {
@@ -1196,6 +1220,9 @@ extern "C" int merl_comm_destroy(merl_comm_t* c) {
     if (!c) return MERL_OK;
     NcclApi* a = nccl_api();
     DeviceGuard g(c->device);
+#if MERL_HAVE_NCCL_DEVICE
+    if (c->dev_comm_state == 1 && a->DevCommDestroy) a->DevCommDestroy(c->comm, &c->dev_comm);
+#endif
     const int rc = (a->ok && c->comm) ? a->CommDestroy(c->comm) : 0;
     delete c;
     return rc ? nccl_fail("ncclCommDestroy", rc) : MERL_OK;
@@ -1244,6 +1271,7 @@ struct merl_peerbuf {
     void* nccl_handle = nullptr;   // NCCL: ncclCommRegister handle
     void* nccl_window = nullptr;   // NCCL: symmetric window
     bool nccl_alloc = false;       // d_buf came from ncclMemAlloc
+    NvlsView nvls{};               // NVLS: multicast / local addresses inside the symmetric window
     const char* registration = "none";
 };
 
@@ -1299,7 +1327,8 @@ void peerbuf_release(merl_peerbuf* b) {
 static int merl_peerbuf_create_impl(merl_comm_t* c, int64_t count, int transport, merl_peerbuf_t** out) {
     MERL_RANGE("merl_peerbuf_create");
     if (!c || !out || count < 1) return fail(MERL_ERR_ARG, "bad argument");
-    if (transport != MERL_XCHG_PEER && transport != MERL_XCHG_NCCL) return fail(MERL_ERR_ARG, "unknown transport %d", transport);
+    if (transport != MERL_XCHG_PEER && transport != MERL_XCHG_NCCL && transport != MERL_XCHG_NVLS)
+        return fail(MERL_ERR_ARG, "unknown transport %d", transport);
     if (c->nranks > kMaxRanks) return fail(MERL_ERR_UNSUPPORTED, "at most %d ranks", kMaxRanks);
     NcclApi* a = nccl_api();
     DeviceGuard g(c->device);
@@ -1317,6 +1346,68 @@ static int merl_peerbuf_create_impl(merl_comm_t* c, int64_t count, int transport
             return bail(fail(e_ == cudaErrorMemoryAllocation ? MERL_ERR_NOMEM : MERL_ERR_CUDA, "%s: %s (%s:%d)", #x, \
                              cudaGetErrorString(e_), __FILE__, __LINE__));                          \
     } while (0)
+    if (transport == MERL_XCHG_NVLS) {
+#if MERL_HAVE_NCCL_DEVICE
+        // symmetric window with a multicast mapping; this library's own kernel does the exchange through it
+        if (!(a->MemAlloc && a->MemFree && a->CommWindowRegister && a->CommWindowDeregister && a->DevCommCreate))
+            return bail(fail(MERL_ERR_UNSUPPORTED, "the loaded NCCL has no symmetric windows / device communicators (needs 2.28+)"));
+        int v = 0;
+        if (a->GetVersion) a->GetVersion(&v);
+        if (v / 100 != NCCL_VERSION_CODE / 100)
+            return bail(fail(MERL_ERR_UNSUPPORTED, "built against NCCL %d headers, running NCCL %d: device structures may differ",
+                             NCCL_VERSION_CODE, v));
+        const size_t data_bytes = (bytes + 4095) & ~(size_t)4095, flag_bytes = sizeof(uint32_t) * 2 * kXchgMaxCtas;
+        if (a->MemAlloc((void**)&b->d_buf, data_bytes + flag_bytes) != 0 || !b->d_buf) {
+            b->d_buf = nullptr;
+            return bail(fail(MERL_ERR_NOMEM, "ncclMemAlloc of %zu bytes failed", data_bytes + flag_bytes));
+        }
+        b->nccl_alloc = true;
+        PB_TRY(cudaMemset(b->d_buf, 0, data_bytes + flag_bytes));
+        PB_TRY(cudaHostAlloc((void**)&b->h_status, sizeof(int), cudaHostAllocMapped));
+        *b->h_status = 0;
+        PB_TRY(cudaHostGetDevicePointer((void**)&b->d_status, b->h_status, 0));
+        PB_TRY(cudaDeviceSynchronize());
+        if (a->CommWindowRegister(c->comm, b->d_buf, data_bytes + flag_bytes, &b->nccl_window, /*NCCL_WIN_COLL_SYMMETRIC*/ 1) != 0 ||
+            !b->nccl_window) {
+            b->nccl_window = nullptr;
+            return bail(fail(MERL_ERR_UNSUPPORTED, "ncclCommWindowRegister(symmetric) failed"));
+        }
+        if (c->dev_comm_state == 0) {
+            ncclDevCommRequirements req{};
+            req.lsaMultimem = true;
+            c->dev_comm_state = a->DevCommCreate(c->comm, &req, &c->dev_comm) == 0 ? 1 : -1;
+        }
+        if (c->dev_comm_state != 1 || !c->dev_comm.lsaMultimem.mcBasePtr || c->dev_comm.lsaSize != c->nranks)
+            return bail(fail(MERL_ERR_UNSUPPORTED, "no multicast mapping over all %d ranks (NVSwitch multicast unavailable, or "
+                             "ranks on several nodes)", c->nranks));
+        ncclWindow_vidmem wv;
+        PB_TRY(cudaMemcpy(&wv, b->nccl_window, sizeof wv, cudaMemcpyDeviceToHost));
+        char* mc = static_cast<char*>(c->dev_comm.lsaMultimem.mcBasePtr) + ((size_t)wv.mcOffset4K << 12);
+        b->nvls.mc_data = reinterpret_cast<float4*>(mc);
+        b->nvls.mc_flags = reinterpret_cast<uint32_t*>(mc + data_bytes);
+        b->nvls.my_flags = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(b->d_buf) + data_bytes);
+        b->nvls.epoch_words = b->nvls.my_flags + kXchgMaxCtas;
+        b->nvls.nranks = c->nranks;
+        b->nvls.rank = c->rank;
+        b->registration = "ncclMemAlloc + symmetric window, own multimem kernel (NVLS)";
+        {
+            int occ = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, nvls_allreduce_kernel<4>, kXchgThreads, 0) != cudaSuccess || occ < 1) occ = 1;
+            cudaGetLastError();
+            int want = 1;   // CTAs per SM: the switch, not the SMs, does the adds
+            if (const char* e = getenv("MERL_NVLS_CTAS_PER_SM")) want = std::max(1, atoi(e));
+            b->ctas_per_sm = std::min(want, occ);
+        }
+        {
+            const int rc = comm_barrier(c);   // every rank has zeroed its flags before anyone arrives
+            if (rc) return bail(rc);
+        }
+        *out = b;
+        return MERL_OK;
+#else
+        return bail(fail(MERL_ERR_UNSUPPORTED, "built without NCCL's device headers (nccl_device/): no MERL_XCHG_NVLS"));
+#endif
+    }
     if (transport == MERL_XCHG_NCCL) {
         // registered buffer: NCCL can then reduce in place out of user memory (no staging copies) and,
         // on NVSwitch systems, use the in-switch reduction with fewer SMs
@@ -1413,7 +1504,7 @@ extern "C" int merl_peerbuf_destroy(merl_peerbuf_t* b) {
             b->opened[p] = false;
         }
     int rc = MERL_OK;
-    if (b->transport == MERL_XCHG_PEER && b->comm->nranks > 1) rc = comm_barrier(b->comm);
+    if (b->transport != MERL_XCHG_NCCL && b->comm->nranks > 1) rc = comm_barrier(b->comm);
     peerbuf_release(b);
     return rc;
 }
@@ -1465,6 +1556,16 @@ extern "C" int merl_peerbuf_allreduce(merl_peerbuf_t* b, int64_t count, const me
     if (*reinterpret_cast<volatile int*>(b->h_status))
         return fail(MERL_ERR_CUDA, "an earlier peer exchange timed out waiting for another rank; the buffer is unusable");
     const float4* mask = mask_table ? mask_table->d_cells : nullptr;
+    if (b->transport == MERL_XCHG_NVLS) {
+        if (b->comm->nranks == 1) {
+            if (mask) { backward_mask_kernel<<<mask_table->num_sms * 8, 256, 0, s>>>(mask, reinterpret_cast<float4*>(b->d_buf), n4); g_launches.fetch_add(1); }
+        } else {
+            nvls_allreduce_kernel<4><<<xchg_grid(b, n4), kXchgThreads, 0, s>>>(b->nvls, n4, mask, b->d_status);
+            g_launches.fetch_add(1);
+        }
+        CUDA_TRY(cudaGetLastError());
+        return MERL_OK;
+    }
     uint32_t* epoch = b->d_flags + kXchgMaxCtas * kMaxRanks;
     const int grid = xchg_grid(b, n4);
     xchg_kernel_for(b->comm->nranks)<<<grid, kXchgThreads, 0, s>>>(b->view, n4, mask, epoch, b->d_status);

@@ -65,9 +65,19 @@ __device__ __forceinline__ void st_peer(float4* p, const float4 v) {
                  : "memory");
 }
 
-// CTA `cta` of every rank meets here.  Every thread fences its own earlier peer stores first.
+// CTA `cta` of every rank meets here.  The CTA barrier orders every thread's earlier peer stores before
+// the flag writers' st.release.sys, and a release is cumulative over what its thread has synchronised
+// with, so no thread needs a fence of its own.  (Round 2's first version had every thread execute
+// __threadfence_system() first: 8 MEMBAR.SC.SYS per CTA and barrier, and a fixed cost of ~70 us per
+// exchange on 8 GPUs whatever the size -- profiles/r02_exchange_n8.txt.  -DMERL_XCHG_THREAD_FENCE=1
+// brings it back for an A/B.)
+#ifndef MERL_XCHG_THREAD_FENCE
+#define MERL_XCHG_THREAD_FENCE 0
+#endif
 __device__ __forceinline__ void xchg_barrier(const PeerView& pv, const int cta, const uint32_t epoch, int* status) {
+#if MERL_XCHG_THREAD_FENCE
     __threadfence_system();
+#endif
     __syncthreads();
     if ((int)threadIdx.x < pv.nranks) {
         const int p = threadIdx.x;
@@ -154,6 +164,80 @@ __global__ void __launch_bounds__(kXchgThreads) peer_allreduce_kernel(const Peer
     }
     xchg_barrier(pv, cta, e0 + 2u, status);
     if (threadIdx.x == 0) epoch_words[cta] = e0 + 2u;
+}
+
+// ---- the same exchange through the NVSwitch (NVLS): multimem.ld_reduce + multimem.st ----------------
+// The buffers of all ranks sit in one NCCL symmetric window (ncclMemAlloc + ncclCommWindowRegister), which
+// also has a MULTICAST mapping: a load-reduce from the multicast address returns the sum of the element
+// over all ranks, formed inside the switch, and a store to it lands in every rank's copy.  Rank r owns
+// slab r as above, but per element it issues ONE 16-byte multimem.ld_reduce (instead of R peer loads)
+// and ONE multimem.st (instead of R peer stores): the link carries (R-1)/R of the buffer out and in per
+// GPU as before, but each GPU only issues 2/R of the requests and the adds happen in the switch.  The
+// validity mask of a deferred-mask backward is applied between the two, as in the peer kernel.
+// Barrier: thread 0 adds 1 to flag `cta` of EVERY rank with one multimem.red.release.sys and waits until
+// its own copy has collected nranks arrivals (the flags live in the same window, after the data).
+__device__ __forceinline__ float4 multimem_ld_reduce(const float4* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st(float4* mc, const float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+struct NvlsView {
+    float4* mc_data;          // multicast address of the window's data
+    uint32_t* mc_flags;       // multicast address of the arrival counters (one per CTA)
+    uint32_t* my_flags;       // this rank's copy of them
+    uint32_t* epoch_words;    // this rank only: arrivals this CTA has already waited for
+    int nranks, rank;
+};
+__device__ __forceinline__ void nvls_barrier(const NvlsView& nv, const int cta, const uint32_t target, int* status) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(nv.mc_flags + cta), "r"(1u) : "memory");
+        const long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys(nv.my_flags + cta) - target) < 0) {
+            if (clock64() - t0 > kXchgTimeoutCycles) { *reinterpret_cast<volatile int*>(status) = 1; break; }
+        }
+    }
+    __syncthreads();
+}
+template <int UNROLL>
+__global__ void __launch_bounds__(kXchgThreads) nvls_allreduce_kernel(const NvlsView nv, const int64_t n4,
+                                                                      const float4* __restrict__ mask_cells,
+                                                                      int* __restrict__ status) {
+    __shared__ uint32_t e_s;
+    const int cta = blockIdx.x;
+    if (threadIdx.x == 0) e_s = nv.epoch_words[cta];
+    __syncthreads();
+    const uint32_t e0 = e_s;
+    const uint32_t R = (uint32_t)nv.nranks;
+    nvls_barrier(nv, cta, e0 + R, status);
+    const int64_t per = (n4 + R - 1) / R;
+    const int64_t lo = min((int64_t)nv.rank * per, n4), hi = min(lo + per, n4);
+    const int64_t step = (int64_t)gridDim.x * kXchgThreads;
+    for (int64_t i0 = lo + (int64_t)cta * kXchgThreads + threadIdx.x; i0 < hi; i0 += step * UNROLL) {
+        float4 acc[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const int64_t i = i0 + u * step;
+            if (i < hi) acc[u] = multimem_ld_reduce(nv.mc_data + i);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const int64_t i = i0 + u * step;
+            if (i >= hi) continue;
+            if (mask_cells) acc[u] = mask_cell(acc[u], __ldg(&reinterpret_cast<const float*>(mask_cells)[4 * i + 3]));
+            multimem_st(nv.mc_data + i, acc[u]);
+        }
+    }
+    nvls_barrier(nv, cta, e0 + 2u * R, status);
+    if (threadIdx.x == 0) nv.epoch_words[cta] = e0 + 2u * R;
 }
 
 }  // namespace merl

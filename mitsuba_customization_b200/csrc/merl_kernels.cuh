@@ -466,7 +466,7 @@ struct SampleOp {
 #define MERL_SAMPLE_STAGE 0
 #endif
 #ifndef MERL_SAMPLE_GUIDE
-#define MERL_SAMPLE_GUIDE 0
+#define MERL_SAMPLE_GUIDE 1
 #endif
     // input staging (see cp_async16): the first use of every streamed input was the kernel's top stall
     // (profiles/r01_sample_ncu_summary.md: long_scoreboard 4.0 of 9 cycles per issue at the first FMUL / FSETP

@@ -99,14 +99,33 @@ __device__ __forceinline__ bool cluster_may_hit(const ClusterBox c, float ox, fl
     return !(tn > tf);
 }
 
-// nearest hit of (o, d) with the spheres in shared memory; returns sphere index or -1
+// Which groups can the ray touch at all?  One bit per group, found with all lanes of the warp in step
+// (the loop has the same trip count for every ray).  The sphere tests then walk each lane's OWN set
+// bits: a warp of incoherent rays pays for the longest candidate list among its lanes, not for the
+// union of the groups any of its lanes touches (the per-group `continue` of round 1 kept lanes idle
+// while a neighbour tested a group they had already rejected: 13 of 32 lanes active in rt_trace_kernel,
+// profiles/r02_render_ncu_summary.md).
+static_assert(kMaxClusters <= 32, "one mask bit per sphere group");
+__device__ __forceinline__ unsigned cluster_mask(const ClusterBox* clus, int n, float ox, float oy, float oz, float dx,
+                                                 float dy, float dz) {
+    const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
+    unsigned mask = 0u;
+    for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize)
+        mask |= cluster_may_hit(clus[k], ox, oy, oz, idx, idy, idz, 3.0e38f) ? (1u << k) : 0u;
+    return mask;
+}
+
+// nearest hit of (o, d) with the spheres in shared memory; returns sphere index or -1.  Groups are
+// visited in index order and a later sphere replaces the best one only when strictly nearer, so the
+// result does not depend on which groups the mask prunes.
 __device__ __forceinline__ int intersect_spheres(const float4* sph, const ClusterBox* clus, int n, float ox, float oy,
                                                  float oz, float dx, float dy, float dz, float& t_hit) {
     int best = -1;
     float tb = 3.0e38f;
-    const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
-    for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize) {
-        if (!cluster_may_hit(clus[k], ox, oy, oz, idx, idy, idz, tb)) continue;
+    unsigned mask = cluster_mask(clus, n, ox, oy, oz, dx, dy, dz);
+    while (mask) {
+        const int s0 = (__ffs(mask) - 1) * kClusterSize;
+        mask &= mask - 1u;
         const int s1 = min(s0 + kClusterSize, n);
         for (int s = s0; s < s1; ++s) {
             const float4 c = sph[s];
@@ -116,11 +135,12 @@ __device__ __forceinline__ int intersect_spheres(const float4* sph, const Cluste
             // cancels catastrophically in fp32 when the origin is many radii away (Ray Tracing Gems ch. 7)
             const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
             const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
-            if (disc < 0.f) continue;
-            const float sq = sqrtf(disc);
+            const float sq = sqrtf(fmaxf(disc, 0.f));
             float t = -b - sq;
             if (t < kRayEps) t = -b + sq;
-            if (t >= kRayEps && t < tb) { tb = t; best = s; }
+            const bool ok = disc >= 0.f && t >= kRayEps && t < tb;   // predicated: no branch per sphere
+            tb = ok ? t : tb;
+            best = ok ? s : best;
         }
     }
     t_hit = tb;
@@ -128,9 +148,11 @@ __device__ __forceinline__ int intersect_spheres(const float4* sph, const Cluste
 }
 __device__ __forceinline__ bool occluded(const float4* sph, const ClusterBox* clus, int n, float ox, float oy, float oz,
                                          float dx, float dy, float dz) {
-    const float idx = 1.f / dx, idy = 1.f / dy, idz = 1.f / dz;
-    for (int k = 0, s0 = 0; s0 < n; ++k, s0 += kClusterSize) {
-        if (!cluster_may_hit(clus[k], ox, oy, oz, idx, idy, idz, 3.0e38f)) continue;
+    unsigned mask = cluster_mask(clus, n, ox, oy, oz, dx, dy, dz);
+    bool any = false;
+    while (mask && !any) {
+        const int s0 = (__ffs(mask) - 1) * kClusterSize;
+        mask &= mask - 1u;
         const int s1 = min(s0 + kClusterSize, n);
         for (int s = s0; s < s1; ++s) {
             const float4 c = sph[s];
@@ -138,12 +160,11 @@ __device__ __forceinline__ bool occluded(const float4* sph, const ClusterBox* cl
             const float b = lx * dx + ly * dy + lz * dz;
             const float qx = fmaf(-b, dx, lx), qy = fmaf(-b, dy, ly), qz = fmaf(-b, dz, lz);
             const float disc = c.w * c.w - (qx * qx + qy * qy + qz * qz);
-            if (disc < 0.f) continue;
-            const float sq = sqrtf(disc);
-            if (-b - sq >= kRayEps || -b + sq >= kRayEps) return true;
+            const float sq = sqrtf(fmaxf(disc, 0.f));
+            any |= disc >= 0.f && (-b - sq >= kRayEps || -b + sq >= kRayEps);
         }
     }
-    return false;
+    return any;
 }
 
 // Duff et al. orthonormal basis (Mitsuba 3's coordinate_system)

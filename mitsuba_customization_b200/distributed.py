@@ -96,15 +96,27 @@ class Comm:
 
 class PeerBuffer:
     """An exchange buffer of `count` floats on this rank's GPU (merl_peerbuf_*): the ranks of `comm` sum
-    it in place with ONE kernel over NVLink peer memory (transport "peer", default) or with ncclAllReduce
-    on a buffer registered with NCCL (transport "nccl").  Creation and destruction are collective.
-    `tensor(shape)` is a zero-copy torch view of the library-owned memory."""
+    it in place with ONE kernel over NVLink peer memory (transport "peer", default), with the library's
+    multimem kernel through the NVSwitch ("nvls": in-switch reduction, NCCL >= 2.28 symmetric window), or
+    with ncclAllReduce on a buffer registered with NCCL ("nccl").  "auto" takes "nvls" when every rank
+    can, else "peer" (the library gives all ranks the same answer, so the choice is collective).
+    Creation and destruction are collective.  `tensor(shape)` is a zero-copy torch view of the
+    library-owned memory."""
 
     def __init__(self, comm: Comm, count: int, transport: str = "peer"):
         self.comm = comm
         self._h = C.c_void_p()
-        kind = {"peer": _cabi.XCHG_PEER, "nccl": _cabi.XCHG_NCCL}[transport]
-        check(_cabi.lib().merl_peerbuf_create(comm._h, int(count), kind, C.byref(self._h)))
+        kinds = {"peer": _cabi.XCHG_PEER, "nccl": _cabi.XCHG_NCCL, "nvls": _cabi.XCHG_NVLS}
+        if transport == "auto":
+            rc = _cabi.lib().merl_peerbuf_create(comm._h, int(count), _cabi.XCHG_NVLS, C.byref(self._h))
+            if rc == _cabi.ERR_UNSUPPORTED:
+                transport = "peer"
+                check(_cabi.lib().merl_peerbuf_create(comm._h, int(count), _cabi.XCHG_PEER, C.byref(self._h)))
+            else:
+                check(rc)
+                transport = "nvls"
+        else:
+            check(_cabi.lib().merl_peerbuf_create(comm._h, int(count), kinds[transport], C.byref(self._h)))
         self.info = _cabi.PeerbufInfo()
         check(_cabi.lib().merl_peerbuf_info(self._h, C.byref(self.info)))
         self.count = int(self.info.count)

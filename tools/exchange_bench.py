@@ -1,5 +1,6 @@
 """Exchange-step microbenchmark under torchrun: in-place sum of a float buffer over the ranks, by size and transport.
   peer             merl_peerbuf_allreduce, MERL_XCHG_PEER (one kernel over NVLink peer memory)
+  nvls             merl_peerbuf_allreduce, MERL_XCHG_NVLS (own multimem.ld_reduce / multimem.st kernel through the switch)
   nccl_registered  merl_peerbuf_allreduce, MERL_XCHG_NCCL (ncclMemAlloc + symmetric window)
   nccl_plain       merl_allreduce_sum_f32 on a torch tensor (round 1's form)
 Prints per size: ms and bus bandwidth 2 (R-1)/R bytes / time, max over ranks."""
@@ -16,6 +17,10 @@ comm = D.Comm(rank, world, local)
 sizes = [1 << 18, 1 << 20, 1 << 22, 5832000, 1 << 24, 1 << 26]   # floats: 1 MB ... 256 MB; 5 832 000 = one gradient table
 cap = max(sizes)
 bufs = {"peer": D.PeerBuffer(comm, cap, "peer"), "nccl_registered": D.PeerBuffer(comm, cap, "nccl")}
+try:
+    bufs["nvls"] = D.PeerBuffer(comm, cap, "nvls")
+except Exception as e:
+    if rank == 0: print("nvls unavailable:", e, flush=True)
 plain = torch.zeros(cap, device=dev)
 
 def timed(fn, it=20):
@@ -41,7 +46,8 @@ for n in sizes:
     row["nccl_plain_bus_gbs"] = 2 * (world - 1) / world * 4 * n / (ms * 1e-3) / 1e9
     rows.append(row)
     if rank == 0:
-        print(f"{4 * n / 1e6:8.1f} MB  peer {row['peer_ms'] * 1e3:8.1f} us ({row['peer_bus_gbs']:6.0f} GB/s)   nccl registered "
+        nv = f"   nvls {row['nvls_ms'] * 1e3:8.1f} us ({row['nvls_bus_gbs']:6.0f})" if "nvls_ms" in row else ""
+        print(f"{4 * n / 1e6:8.1f} MB  peer {row['peer_ms'] * 1e3:8.1f} us ({row['peer_bus_gbs']:6.0f} GB/s){nv}   nccl registered "
               f"{row['nccl_registered_ms'] * 1e3:8.1f} us ({row['nccl_registered_bus_gbs']:6.0f})   nccl plain {row['nccl_plain_ms'] * 1e3:8.1f} us "
               f"({row['nccl_plain_bus_gbs']:6.0f})", flush=True)
 # correctness at the largest size
