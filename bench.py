@@ -386,10 +386,27 @@ def run_b200(args):
                                       "min": min(per), "median": sorted(per)[ks // 2], "steps": ks}
         u1, u2 = torch.rand(n, device=dev, generator=gen), torch.rand(2, n, device=dev, generator=gen)
         k = max(3, min(args.steps, 20))
+
+        def sm_clock():
+            try:
+                return int(sampler.nv.nvmlDeviceGetClockInfo(sampler.h, sampler.nv.NVML_CLOCK_SM))
+            except Exception:
+                return None
+        # the sampler is issue-bound, so it follows the SM clock: measured (a) right after the 200-step eval+pdf
+        # hold above, i.e. under the power cap that hold provokes (this is the state round 1's 57 Gquery/s on the
+        # scaling node came from), and (b) after an idle period, as tools/one_kernel.py measures it
+        ms_h, _ = timed(lambda: plug.sample(ctx, si, u1, u2), k, 3)
+        clk_h = sm_clock()
+        torch.cuda.synchronize()
+        time.sleep(1.0)
         ms_s, _ = timed(lambda: plug.sample(ctx, si, u1, u2), k, 3)
+        clk_s = sm_clock()
         extras["sample_gquery_s"] = world * n / (ms_s / k * 1e-3) / 1e9
         extras["sample_hbm_gbs_per_gpu"] = 56 * n / (ms_s / k * 1e-3) / 1e9
         extras["sample_frac_of_hbm"] = extras["sample_hbm_gbs_per_gpu"] / peak
+        extras["sample_states"] = {"after_idle": {"gquery_s_per_gpu": n / (ms_s / k * 1e-3) / 1e9, "sm_mhz_at_end": clk_s},
+                                   "after_200_step_eval_pdf_hold": {"gquery_s_per_gpu": n / (ms_h / k * 1e-3) / 1e9,
+                                                                    "sm_mhz_at_end": clk_h}}
         # BASELINE config 1 on the GPU: 2^20 pairs, eval+pdf then sample (launch-latency dominated: 42 MB is
         # ~6 us at the roofline; reported, not used for any roofline fraction)
         m20 = 1 << 20

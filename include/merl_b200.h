@@ -214,7 +214,7 @@ typedef struct merl_render_params {
     int32_t spp_total;         /* normalisation                                         */
     int32_t spp_begin, spp_end;/* sample indices this call renders for every pixel       */
     int32_t max_depth;         /* surface interactions per path (>= 1)                   */
-    int32_t wavefront;         /* paths per pass; 0 = 1 << 23 (2 GB of workspace) */
+    int32_t wavefront;         /* paths per pass (264 B of workspace each); 0 = up to 1 << 26, at most 1/4 of the free device memory */
     int32_t reserved;
     uint64_t seed;
     float cam_pos[3], cam_target[3], cam_up[3];

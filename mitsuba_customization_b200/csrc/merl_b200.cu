@@ -1272,6 +1272,7 @@ struct merl_peerbuf {
     void* nccl_window = nullptr;   // NCCL: symmetric window
     bool nccl_alloc = false;       // d_buf came from ncclMemAlloc
     NvlsView nvls{};               // NVLS: multicast / local addresses inside the symmetric window
+    int nvls_grid_cap = 0, nvls_unroll = 4;   // tuning knobs (MERL_NVLS_GRID, MERL_NVLS_UNROLL)
     const char* registration = "none";
 };
 
@@ -1397,6 +1398,8 @@ static int merl_peerbuf_create_impl(merl_comm_t* c, int64_t count, int transport
             int want = 1;   // CTAs per SM: the switch, not the SMs, does the adds
             if (const char* e = getenv("MERL_NVLS_CTAS_PER_SM")) want = std::max(1, atoi(e));
             b->ctas_per_sm = std::min(want, occ);
+            if (const char* e = getenv("MERL_NVLS_GRID")) b->nvls_grid_cap = std::max(1, atoi(e));
+            if (const char* e = getenv("MERL_NVLS_UNROLL")) b->nvls_unroll = atoi(e);
         }
         {
             const int rc = comm_barrier(c);   // every rank has zeroed its flags before anyone arrives
@@ -1560,7 +1563,11 @@ extern "C" int merl_peerbuf_allreduce(merl_peerbuf_t* b, int64_t count, const me
         if (b->comm->nranks == 1) {
             if (mask) { backward_mask_kernel<<<mask_table->num_sms * 8, 256, 0, s>>>(mask, reinterpret_cast<float4*>(b->d_buf), n4); g_launches.fetch_add(1); }
         } else {
-            nvls_allreduce_kernel<4><<<xchg_grid(b, n4), kXchgThreads, 0, s>>>(b->nvls, n4, mask, b->d_status);
+            int grid = xchg_grid(b, n4);
+            if (b->nvls_grid_cap > 0) grid = std::min(grid, b->nvls_grid_cap);
+            if (b->nvls_unroll == 8) nvls_allreduce_kernel<8><<<grid, kXchgThreads, 0, s>>>(b->nvls, n4, mask, b->d_status);
+            else if (b->nvls_unroll == 2) nvls_allreduce_kernel<2><<<grid, kXchgThreads, 0, s>>>(b->nvls, n4, mask, b->d_status);
+            else nvls_allreduce_kernel<4><<<grid, kXchgThreads, 0, s>>>(b->nvls, n4, mask, b->d_status);
             g_launches.fetch_add(1);
         }
         CUDA_TRY(cudaGetLastError());
@@ -1691,6 +1698,7 @@ static int merl_render_impl(const merl_table_t* const* tables, int ntables, cons
     if (p->width < 1 || p->height < 1 || p->max_depth < 1 || p->spp_total < 1 || p->spp_begin < 0 ||
         p->spp_end < p->spp_begin || p->spp_end > p->spp_total)
         return fail(MERL_ERR_ARG, "bad render parameters");
+    if (p->spp_total > (1 << 22)) return fail(MERL_ERR_ARG, "spp_total must not exceed 2^22 (the sample index shares a queue word)");
     if (!aligned(film4, 16)) return fail(MERL_ERR_ARG, "film4 must be 16-byte aligned");
     // by-table sharding: this rank evaluates tables m with m % own_world == own_rank only
     const int own_world = p->table_shard_world > 1 ? p->table_shard_world : 1;
@@ -1732,7 +1740,18 @@ static int merl_render_impl(const merl_table_t* const* tables, int ntables, cons
     const int64_t npix = (int64_t)p->width * p->height;
     const int64_t total = npix * (p->spp_end - p->spp_begin);
     if (total == 0) { if (stats_out) memset(stats_out, 0, sizeof *stats_out); return MERL_OK; }
-    int64_t cap = p->wavefront > 0 ? p->wavefront : (1 << 23);   // 8 Mi paths: 2 GB of workspace, kept in the pool
+    // Paths per pass.  Default: as many as fit comfortably, up to 64 Mi (264 B of workspace per path = 17.7 GB of
+    // a B200's 180 GB, kept in the pool): the late bounces of a pass hold a few percent of the paths but cost
+    // six launches at their latency floor each, so fewer, fatter passes are faster -- config 5 (268 M paths):
+    // 4873 / 5515 / 5850 / 6019 spp Mpix/s at 8 / 16 / 32 / 64 Mi paths per pass (profiles/r02_render_wavefront.txt).
+    // The default stays below a quarter of the device memory that is free right now.
+    int64_t cap = p->wavefront;
+    if (cap <= 0) {
+        cap = (int64_t)1 << 26;
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); free_b = (size_t)8 << 30; }
+        while (cap > (1 << 20) && (size_t)cap * 264 > free_b / 4) cap >>= 1;
+    }
     if (cap > total) cap = total;
     cap = (cap + 255) & ~(int64_t)255;
     if (own_world > 1) {

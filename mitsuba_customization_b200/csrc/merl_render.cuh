@@ -262,58 +262,125 @@ struct LiveList {
     int* count_out;        // zeroed by rt_scan_kernel of the same bounce
 };
 
-// Returns true when path i has a BSDF query this bounce.  PRIMARY: the camera ray is generated in
-// registers (depth 0) and path state is written only for the rays that hit a surface; a camera ray
-// that escapes costs one film update and no path-state traffic.
+// A bounce's trace step runs in two halves with a shared-memory queue between them, so that each half
+// executes with full warps.  FRONT: intersect; a ray that escapes (or has used its interaction budget)
+// is finished on the spot, a ray that hits is pushed onto the CTA's queue.  BACK (once 256 hits are
+// queued, and for the rest at the end): surface frame, the interaction's Philox draw, the shadow ray,
+// the BSDF-stage inputs.  In one piece the second half ran at the hit rate: after a bounce about half of
+// the rays escape, and rt_trace_kernel executed with 13 of 32 lanes active (profiles/r02_render_ncu_summary.md).
+constexpr int kHitQueue = 512;   // < 256 left over + 256 pushed per iteration
+struct HitQueue {
+    float4 d[kHitQueue];   // ray direction
+    int i[kHitQueue];      // path index
+    int hit[kHitQueue];    // sphere
+    float t[kHitQueue];
+    int n;                 // slot allocator (the CTA-uniform count lives in a register of every thread)
+};
+
+// PRIMARY: the camera ray is generated in registers (depth 0) and path state is written only for the
+// rays that hit a surface; a camera ray that escapes costs one film update and no path-state traffic.
+// Every thread of the CTA calls it (in_range = false: nothing to trace); returns whether it pushed.
 template <bool PRIMARY>
-__device__ __forceinline__ bool trace_one(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
-                                          const ClusterBox* clus, const int* smat, const int i, const int depth,
-                                          const int64_t first, float4* __restrict__ film, int* hist) {
+__device__ __forceinline__ bool trace_front(const RenderDev& R, const PathState& P, const float4* sph,
+                                            const ClusterBox* clus, const int i, const bool in_range, const int depth,
+                                            const int64_t first, float4* __restrict__ film, HitQueue& hq) {
+    static_assert(kMaxSpheres <= 256, "the sphere index shares a queue word with the sample index");
+    bool push = false;
+    int hit = -1, pixel_q = 0, smp_q = 0;
+    float t = 0.f;
+    float4 d4 = make_float4(0.f, 0.f, 1.f, 0.f);
+    if (in_range) {
+        int pixel, smp;
+        float4 o4;
+        bool alive = true;
+        if (PRIMARY) {
+            camera_ray(R, first + i, pixel, smp, o4, d4);
+        } else {
+            pixel = P.pixel[i];
+            if (pixel < 0) { P.mat[i] = -1; alive = false; }
+            else { o4 = P.org[i]; d4 = P.dir[i]; }
+        }
+        if (alive) {
+            hit = intersect_spheres(sph, clus, R.nspheres, o4.x, o4.y, o4.z, d4.x, d4.y, d4.z, t);
+            if (hit < 0 || depth >= R.max_depth) {
+                float lr = 0.f, lg = 0.f, lb = 0.f;
+                if (!PRIMARY) { const float4 l4 = P.rad[i]; lr = l4.x; lg = l4.y; lb = l4.z; }
+                if (hit < 0) {
+                    // escaped: environment radiance, MIS against the emitter sample of the previous bounce
+                    const float w = depth == 0 ? 1.f : power_heuristic(o4.w, 0.0795774715f);
+                    const float4 t4 = PRIMARY ? make_float4(1.f, 1.f, 1.f, 0.f) : P.thr[i];
+                    lr = fmaf(t4.x * R.env[0], w, lr); lg = fmaf(t4.y * R.env[1], w, lg); lb = fmaf(t4.z * R.env[2], w, lb);
+                }   // else: interaction budget used up
+                film_add(film, pixel, lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
+                if (!PRIMARY) { P.pixel[i] = -1; P.mat[i] = -1; }
+            } else {
+                push = true;
+                if (PRIMARY) { pixel_q = pixel; smp_q = smp; }
+            }
+        }
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, push);
+    if (b) {
+        const int lane = threadIdx.x & 31, leader = __ffs(b) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&hq.n, __popc(b));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (push) {
+            const int slot = base + __popc(b & ((1u << lane) - 1u));
+            MERL_CHECK(slot >= 0 && slot < kHitQueue);
+            // PRIMARY: pixel and sample index ride along (d.w, upper bits of the sphere index) so that the
+            // second half does not repeat the 64-bit division of the global sample index
+            if (PRIMARY) { d4.w = __int_as_float(pixel_q); hit |= smp_q << 8; }
+            hq.d[slot] = d4; hq.i[slot] = i; hq.hit[slot] = hit; hq.t[slot] = t;
+        }
+    }
+    return push;
+}
+
+// Second half for queue slot `slot` (valid = false: this thread has none).  Returns true when the path
+// has a BSDF query this bounce; path_out = its index.
+template <bool PRIMARY>
+__device__ __forceinline__ bool trace_back(const RenderDev& R, const PathState& P, const StageBuf& S, const float4* sph,
+                                           const ClusterBox* clus, const int* smat, const HitQueue& hq, const int slot,
+                                           const bool valid, const int depth, const int64_t first,
+                                           float4* __restrict__ film, int* hist, int& path_out) {
+    if (!valid) return false;
+    const float4 d4 = hq.d[slot];
+    const int i = hq.i[slot];
+    int hit = hq.hit[slot];
+    const float t = hq.t[slot];
+    path_out = i;
     int pixel, smp;
-    float4 o4, d4;
+    float ox, oy, oz;
     if (PRIMARY) {
-        camera_ray(R, first + i, pixel, smp, o4, d4);
+        pixel = __float_as_int(d4.w);
+        smp = hit >> 8;
+        hit &= 255;
+        ox = R.cam.px; oy = R.cam.py; oz = R.cam.pz;
     } else {
-        pixel = P.pixel[i];
-        if (pixel < 0) { P.mat[i] = -1; return false; }
-        o4 = P.org[i]; d4 = P.dir[i];
+        pixel = P.pixel[i]; smp = P.sample[i];
+        const float4 o4 = P.org[i];
+        ox = o4.x; oy = o4.y; oz = o4.z;
     }
-    const float ox = o4.x, oy = o4.y, oz = o4.z, dx = d4.x, dy = d4.y, dz = d4.z;
-    float t;
-    const int hit = intersect_spheres(sph, clus, R.nspheres, ox, oy, oz, dx, dy, dz, t);
-    bool finish = false;
-    float lr = 0.f, lg = 0.f, lb = 0.f;
-    if (!PRIMARY) { const float4 l4 = P.rad[i]; lr = l4.x; lg = l4.y; lb = l4.z; }
-    if (hit < 0) {
-        // escaped: environment radiance, MIS against the emitter sample of the previous bounce
-        const float w = depth == 0 ? 1.f : power_heuristic(o4.w, 0.0795774715f);
-        const float4 t4 = PRIMARY ? make_float4(1.f, 1.f, 1.f, 0.f) : P.thr[i];
-        lr = fmaf(t4.x * R.env[0], w, lr); lg = fmaf(t4.y * R.env[1], w, lg); lb = fmaf(t4.z * R.env[2], w, lb);
-        finish = true;
-    } else if (depth >= R.max_depth) {
-        finish = true;   // interaction budget used up
-    }
-    float wix = 0.f, wiy = 0.f, wiz = -1.f, nx = 0.f, ny = 0.f, nz = 1.f, hx = 0.f, hy = 0.f, hz = 0.f;
+    const float dx = d4.x, dy = d4.y, dz = d4.z;
+    const float4 c = sph[hit];
+    const float hx = fmaf(t, dx, ox), hy = fmaf(t, dy, oy), hz = fmaf(t, dz, oz);
+    const float ir = 1.f / c.w;
+    float nx = (hx - c.x) * ir, ny = (hy - c.y) * ir, nz = (hz - c.z) * ir;
+    const float inv = rsqrtf(nx * nx + ny * ny + nz * nz);
+    nx *= inv; ny *= inv; nz *= inv;
     float s[3], tt[3];
-    if (!finish) {
-        const float4 c = sph[hit];
-        hx = fmaf(t, dx, ox); hy = fmaf(t, dy, oy); hz = fmaf(t, dz, oz);
-        const float ir = 1.f / c.w;
-        nx = (hx - c.x) * ir; ny = (hy - c.y) * ir; nz = (hz - c.z) * ir;
-        const float inv = rsqrtf(nx * nx + ny * ny + nz * nz);
-        nx *= inv; ny *= inv; nz *= inv;
-        frame_from_normal(nx, ny, nz, s, tt);
-        wix = -(dx * s[0] + dy * s[1] + dz * s[2]);
-        wiy = -(dx * tt[0] + dy * tt[1] + dz * tt[2]);
-        wiz = -(dx * nx + dy * ny + dz * nz);
-        if (!(wiz > 0.f)) finish = true;   // grazing / inside hit: nothing to shade
-    }
-    if (finish) {
+    frame_from_normal(nx, ny, nz, s, tt);
+    const float wix = -(dx * s[0] + dy * s[1] + dz * s[2]);
+    const float wiy = -(dx * tt[0] + dy * tt[1] + dz * tt[2]);
+    const float wiz = -(dx * nx + dy * ny + dz * nz);
+    if (!(wiz > 0.f)) {   // grazing / inside hit: nothing to shade
+        float lr = 0.f, lg = 0.f, lb = 0.f;
+        if (!PRIMARY) { const float4 l4 = P.rad[i]; lr = l4.x; lg = l4.y; lb = l4.z; }
         film_add(film, pixel, lr * R.inv_spp, lg * R.inv_spp, lb * R.inv_spp, R.inv_spp);
         if (!PRIMARY) { P.pixel[i] = -1; P.mat[i] = -1; }
         return false;
     }
-    if (!PRIMARY) smp = P.sample[i];
     // ONE Philox call per surface interaction: four 24-bit uniforms from the high bits of its words (emitter
     // direction, lobe choice, first BSDF number) and a fifth from the low bytes u01() does not use
     uint32_t re[4];
@@ -384,12 +451,30 @@ __global__ void __launch_bounds__(256) rt_primary_kernel(const RenderDev R, cons
     if (blockIdx.x * blockDim.x >= np) return;
     stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat, hist, R.ntables);
     __shared__ int s_warp[kAppendWarps];
+    __shared__ HitQueue hq;
+    if (threadIdx.x == 0) hq.n = 0;
+    __syncthreads();
+    int nq = 0;   // queued hits, the same in every thread
     for (int j0 = blockIdx.x * blockDim.x; j0 < np; j0 += gridDim.x * blockDim.x) {   // CTA-uniform trip count
         const int i = j0 + threadIdx.x;
-        const bool q = i < np && trace_one<true>(R, P, S, sc.sph, sc.clus, sc.smat, i, 0, first, film, hist);
+        const bool pushed = trace_front<true>(R, P, sc.sph, sc.clus, i, i < np, 0, first, film, hq);
+        nq += __syncthreads_count(pushed);
+        if (nq >= 256) {
+            nq -= 256;
+            if (threadIdx.x == 0) hq.n = nq;   // (ordered before the next pushes by cta_append's barriers)
+            int path = 0;
+            const bool q = trace_back<true>(R, P, S, sc.sph, sc.clus, sc.smat, hq, nq + threadIdx.x, true, 0, first, film, hist, path);
+            const int dst = cta_append(q, live_count, s_warp);
+            MERL_CHECK(!q || (dst >= 0 && dst < np));
+            if (q) live_out[dst] = path;
+        }
+    }
+    if (nq > 0) {
+        int path = 0;
+        const bool q = trace_back<true>(R, P, S, sc.sph, sc.clus, sc.smat, hq, threadIdx.x, (int)threadIdx.x < nq, 0, first, film, hist, path);
         const int dst = cta_append(q, live_count, s_warp);
         MERL_CHECK(!q || (dst >= 0 && dst < np));
-        if (q) live_out[dst] = i;
+        if (q) live_out[dst] = path;
     }
     flush_hist(hist, R.ntables, counts);
 }
@@ -408,10 +493,27 @@ __global__ void __launch_bounds__(256) rt_trace_kernel(const RenderDev R, const 
     if (blockIdx.x * blockDim.x >= count) return;          // whole CTA beyond the live range
     stage_scene(sc, R.nspheres, spheres, clusters, sphere_mat, hist, R.ntables);
     MERL_CHECK(count >= 0 && count <= pass->np);
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
-        const int i = L.in[j];
+    __shared__ HitQueue hq;
+    if (threadIdx.x == 0) hq.n = 0;
+    __syncthreads();
+    int nq = 0;
+    for (int j0 = blockIdx.x * blockDim.x; j0 < count; j0 += gridDim.x * blockDim.x) {   // CTA-uniform trip count
+        const int j = j0 + threadIdx.x;
+        const int i = j < count ? L.in[j] : 0;
         MERL_CHECK(i >= 0 && i < pass->np);
-        trace_one<false>(R, P, S, sc.sph, sc.clus, sc.smat, i, depth, 0, film, hist);
+        const bool pushed = trace_front<false>(R, P, sc.sph, sc.clus, i, j < count, depth, 0, film, hq);
+        nq += __syncthreads_count(pushed);
+        if (nq >= 256) {
+            nq -= 256;
+            if (threadIdx.x == 0) hq.n = nq;
+            int path = 0;
+            trace_back<false>(R, P, S, sc.sph, sc.clus, sc.smat, hq, nq + threadIdx.x, true, depth, 0, film, hist, path);
+            __syncthreads();   // everyone has read its slot and sees the new hq.n before the next pushes
+        }
+    }
+    if (nq > 0) {
+        int path = 0;
+        trace_back<false>(R, P, S, sc.sph, sc.clus, sc.smat, hq, threadIdx.x, (int)threadIdx.x < nq, depth, 0, film, hist, path);
     }
     flush_hist(hist, R.ntables, counts);
 }

@@ -15,8 +15,10 @@ dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 comm = D.Comm(rank, world, local)
 sizes = [1 << 18, 1 << 20, 1 << 22, 5832000, 1 << 24, 1 << 26]   # floats: 1 MB ... 256 MB; 5 832 000 = one gradient table
+only = os.environ.get("XCHG_ONLY", "")            # e.g. XCHG_ONLY=nvls: that transport alone, three sizes (tuning sweeps)
+if only: sizes = [1 << 20, 5832000, 1 << 24]
 cap = max(sizes)
-bufs = {"peer": D.PeerBuffer(comm, cap, "peer"), "nccl_registered": D.PeerBuffer(comm, cap, "nccl")}
+bufs = {} if only else {"peer": D.PeerBuffer(comm, cap, "peer"), "nccl_registered": D.PeerBuffer(comm, cap, "nccl")}
 try:
     bufs["nvls"] = D.PeerBuffer(comm, cap, "nvls")
 except Exception as e:
@@ -41,6 +43,10 @@ for n in sizes:
         ms = timed(lambda: pb.allreduce_(count=n))
         row[name + "_ms"] = ms
         row[name + "_bus_gbs"] = 2 * (world - 1) / world * 4 * n / (ms * 1e-3) / 1e9
+    if only:
+        rows.append(row)
+        if rank == 0: print(f"{4 * n / 1e6:8.1f} MB  " + "  ".join(f"{k[:-3]} {v * 1e3:7.1f} us" for k, v in row.items() if k.endswith("_ms")), flush=True)
+        continue
     ms = timed(lambda: comm.allreduce_sum_(plain[:n]))
     row["nccl_plain_ms"] = ms
     row["nccl_plain_bus_gbs"] = 2 * (world - 1) / world * 4 * n / (ms * 1e-3) / 1e9

@@ -34,6 +34,9 @@ def main():
             print(f"# {ntab} tables built in {time.time() - t0:.1f} s, "
                   f"{sum(p.info.table_bytes for p in plugs) / 1e9:.2f} GB of float4 cells", file=sys.stderr)
     rng = RD.spp_share(spp, world, rank)
+    emu = int(os.environ.get("RD_EMULATE_WORLD", "0"))   # one GPU doing rank 0's share of an `emu`-GPU render (time split of a rank)
+    if emu > 1 and world == 1:
+        rng = RD.spp_share(spp, emu, 0)
     wf = int(os.environ.get("MERL_WAVEFRONT", "0"))   # paths per pass; 0 = the library's default
     film = torch.zeros(h, w, 4, device=dev)
 
@@ -61,7 +64,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     _, st = RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=rng, want_stats=True, wavefront=wf)
-    out = {"config": cfg, "n_gpus": world, "wavefront": wf or (1 << 23), "width": w, "height": h, "spp": spp, "max_depth": depth, "ms": ms,
+    out = {"config": cfg, "n_gpus": world, "wavefront": wf or "library default (up to 2^26 paths per pass)", "width": w, "height": h, "spp": spp, "max_depth": depth, "ms": ms,
            "spp_mpix_per_s": spp * w * h / 1e6 / (ms * 1e-3), "paths_per_rank": st["paths"],
            "bsdf_queries_per_rank": st["bsdf_queries"], "launches_per_rank": st["launches"],
            "mean_radiance": [float(x) for x in film[..., :3].mean(dim=(0, 1))],
