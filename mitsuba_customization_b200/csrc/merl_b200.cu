@@ -1272,7 +1272,11 @@ struct merl_peerbuf {
     void* nccl_window = nullptr;   // NCCL: symmetric window
     bool nccl_alloc = false;       // d_buf came from ncclMemAlloc
     NvlsView nvls{};               // NVLS: multicast / local addresses inside the symmetric window
-    int nvls_grid_cap = 0, nvls_unroll = 4;   // tuning knobs (MERL_NVLS_GRID, MERL_NVLS_UNROLL)
+    // 32 CTAs x 256 threads x 4 = 32 Ki 16-byte requests in flight per GPU is where the switch path peaks; more
+    // CTAs or deeper unrolling only queue up in front of the link (profiles/r02_nvls_sweep_n8.txt: 23.3 MB on 8
+    // GPUs in 71.7 us at 32 x 4 against 84.9 us at 148 x 4; NCCL's own kernel uses 3 CTAs x 512 threads).
+    // MERL_NVLS_GRID / MERL_NVLS_UNROLL override at buffer creation (tuning).
+    int nvls_grid_cap = 32, nvls_unroll = 4;
     const char* registration = "none";
 };
 
