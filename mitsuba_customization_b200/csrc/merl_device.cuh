@@ -98,100 +98,48 @@ __device__ __forceinline__ float rcp_approx(float x) {
     float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
 }
 
-// ---- one query (float) or a PAIR of queries (float2) per lane ---------------------------------------
-// sm_100 has packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2: two IEEE fp32 results per instruction and
-// lane, the same rounding as the scalar forms, half the issue slots; measured on B200 at the scalar FMA
-// rate and latency, tools/probe/ffma2_probe.cu, profiles/r02_ffma2_probe.txt).  The streaming kernels hold
-// four queries per lane, so the multiply/add/fma backbone of the bin math is written once over
-// T = float | float2 and the 4-wide loops run it on two pairs.  Everything with an operand modifier or no
-// packed form (abs, min/max, saturate, MUFU, compares, selects, float->int) stays per component.  Every
-// product and sum is an explicit round-to-nearest operation (never contracted by the compiler), so a query
-// gives the same bits whichever width it went through: 4-wide, tail, AoS and redo paths stay bit-identical.
-template <class T> __device__ __forceinline__ T p_set(float c);
-template <> __device__ __forceinline__ float p_set<float>(float c) { return c; }
-template <> __device__ __forceinline__ float2 p_set<float2>(float c) { return make_float2(c, c); }
-
-__device__ __forceinline__ float p_mul(float a, float b) { return __fmul_rn(a, b); }
-__device__ __forceinline__ float p_add(float a, float b) { return __fadd_rn(a, b); }
-__device__ __forceinline__ float p_sub(float a, float b) { return __fsub_rn(a, b); }
-__device__ __forceinline__ float p_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
-__device__ __forceinline__ float p_neg(float a) { return -a; }
-__device__ __forceinline__ float2 p_mul(float2 a, float2 b) { return __fmul2_rn(a, b); }
-__device__ __forceinline__ float2 p_add(float2 a, float2 b) { return __fadd2_rn(a, b); }
-__device__ __forceinline__ float2 p_sub(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.f, -1.f), a); }   // a - b, one rounding
-__device__ __forceinline__ float2 p_fma(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
-__device__ __forceinline__ float2 p_neg(float2 a) { return __fmul2_rn(a, make_float2(-1.f, -1.f)); }               // exact
-
-// per-component operations
-#define MERL_P1(name, expr)                                                                          \
-    __device__ __forceinline__ float name(float a) { return expr(a); }                               \
-    __device__ __forceinline__ float2 name(float2 a) { return make_float2(expr(a.x), expr(a.y)); }
-MERL_P1(p_abs, fabsf)
-MERL_P1(p_sqrt, sqrt_approx)
-MERL_P1(p_rsqrt, rsqrt_approx)
-MERL_P1(p_rcp, rcp_approx)
-#undef MERL_P1
-__device__ __forceinline__ float p_max(float a, float c) { return fmaxf(a, c); }
-__device__ __forceinline__ float2 p_max(float2 a, float c) { return make_float2(fmaxf(a.x, c), fmaxf(a.y, c)); }
-__device__ __forceinline__ float p_mul_sat(float a, float b) { return __saturatef(__fmul_rn(a, b)); }
-__device__ __forceinline__ float2 p_mul_sat(float2 a, float2 b) {
-    return make_float2(__saturatef(__fmul_rn(a.x, b.x)), __saturatef(__fmul_rn(a.y, b.y)));
-}
-
 // ---- candidate polynomials (accuracy requirement: |error| << 0.5 bin) ----
-template <class T> __device__ __forceinline__ T acos_poly(T x) {
-    return p_fma(p_fma(p_fma(p_set<T>(-0.02087747f), x, p_set<T>(0.07687739f)), x, p_set<T>(-0.21286782f)), x,
-                 p_set<T>(1.57075773f));
-}
-// acos(x), x already clamped to [0,1]: sqrt(1-x)*cubic, max abs. error 3.9e-5 rad.
-template <class T> __device__ __forceinline__ T fast_acos01_t(T x) {
-    return p_mul(p_sqrt(p_sub(p_set<T>(1.f), x)), acos_poly(x));
-}
-// acos(x) on [0,1] given 1 - x computed without cancellation (relative error 2.3e-4 as x -> 1).
-template <class T> __device__ __forceinline__ T fast_acos01_om_t(T x, T one_minus_x) {
-    return p_mul(p_sqrt(p_max(one_minus_x, 0.f)), acos_poly(x));
-}
 // atan(y/x) for y >= 0, any x: 4-term odd minimax, max rel. error 1.9e-4.
-__device__ __forceinline__ float atan_fold(float r, float y, float ax, float x) {
-    r = (y > ax) ? __fsub_rn(1.57079633f, r) : r;
-    return (x < 0.f) ? __fsub_rn(3.14159265f, r) : r;
-}
-__device__ __forceinline__ float fast_atan2_pos_t(float y, float x) {
+__device__ __forceinline__ float fast_atan2_pos(float y, float x) {
     const float ax = fabsf(x);
     const float mx = fmaxf(ax, y), mn = fminf(ax, y);
-    const float a = p_mul(mn, rcp_approx(fmaxf(mx, 1e-37f)));
-    const float a2 = p_mul(a, a);
-    const float r = p_mul(p_fma(p_fma(p_fma(-0.04508537f, a2, 0.15670808f), a2, -0.32622819f), a2, 0.9998109f), a);
-    return atan_fold(r, y, ax, x);
+    const float a = mn * rcp_approx(fmaxf(mx, 1e-37f));
+    const float a2 = a * a;
+    float r = fmaf(fmaf(fmaf(-0.04508537f, a2, 0.15670808f), a2, -0.32622819f), a2, 0.9998109f) * a;
+    r = (y > ax) ? 1.57079633f - r : r;
+    return (x < 0.f) ? 3.14159265f - r : r;
 }
-__device__ __forceinline__ float2 fast_atan2_pos_t(float2 y, float2 x) {
-    typedef float2 T;
-    const float2 ax = p_abs(x);
-    const float2 mx = make_float2(fmaxf(ax.x, y.x), fmaxf(ax.y, y.y)), mn = make_float2(fminf(ax.x, y.x), fminf(ax.y, y.y));
-    const float2 a = p_mul(mn, p_rcp(p_max(mx, 1e-37f)));
-    const float2 a2 = p_mul(a, a);
-    const float2 r = p_mul(p_fma(p_fma(p_fma(p_set<T>(-0.04508537f), a2, p_set<T>(0.15670808f)), a2, p_set<T>(-0.32622819f)), a2,
-                                 p_set<T>(0.9998109f)), a);
-    return make_float2(atan_fold(r.x, y.x, ax.x, x.x), atan_fold(r.y, y.y, ax.y, x.y));
+// acos(x) on [0,1]: sqrt(1-x)*cubic, max abs. error 3.9e-5 rad.
+__device__ __forceinline__ float fast_acos01(float x) {
+    x = fminf(fmaxf(x, 0.f), 1.f);
+    const float p = fmaf(fmaf(fmaf(-0.02087747f, x, 0.07687739f), x, -0.21286782f), x, 1.57075773f);
+    return sqrt_approx(1.f - x) * p;
+}
+
+// acos(x) on [0,1] given 1 - x computed without cancellation (relative error 2.3e-4 as x -> 1).
+__device__ __forceinline__ float fast_acos01_om(float x, float one_minus_x) {
+    const float p = fmaf(fmaf(fmaf(-0.02087747f, x, 0.07687739f), x, -0.21286782f), x, 1.57075773f);
+    return sqrt_approx(fmaxf(one_minus_x, 0.f)) * p;
 }
 
 struct Bins {
     int ih, id, ip;
 };
 
-// Quantities of one query (or pair) shared by binning, pdf and the slow tiers.
-template <class T> struct HalfDiffT { T sx, sy, sz, rho2, n2, A, inv_s, slen; };
-typedef HalfDiffT<float> HalfDiff;
+// Quantities of one query shared by binning, pdf and the slow tiers.
+struct HalfDiff {
+    float sx, sy, sz, rho2, n2, A, inv_s, slen;
+};
 
-template <class T>
-__device__ __forceinline__ HalfDiffT<T> half_diff_setup(T ax, T ay, T az, T bx, T by, T bz) {
-    HalfDiffT<T> h;
-    h.sx = p_add(ax, bx); h.sy = p_add(ay, by); h.sz = p_add(az, bz);
-    h.rho2 = p_fma(h.sx, h.sx, p_mul(h.sy, h.sy));
-    h.n2 = p_fma(h.sz, h.sz, h.rho2);
-    h.A = p_fma(ax, h.sx, p_fma(ay, h.sy, p_mul(az, h.sz)));
-    h.inv_s = p_rsqrt(p_max(h.n2, 1e-37f));
-    h.slen = p_mul(h.n2, h.inv_s);
+__device__ __forceinline__ HalfDiff half_diff_setup(float ax, float ay, float az, float bx, float by,
+                                                    float bz) {
+    HalfDiff h;
+    h.sx = ax + bx; h.sy = ay + by; h.sz = az + bz;
+    h.rho2 = fmaf(h.sx, h.sx, h.sy * h.sy);
+    h.n2 = fmaf(h.sz, h.sz, h.rho2);
+    h.A = fmaf(ax, h.sx, fmaf(ay, h.sy, az * h.sz));
+    h.inv_s = rsqrt_approx(fmaxf(h.n2, 1e-37f));
+    h.slen = h.n2 * h.inv_s;
     return h;
 }
 
@@ -205,19 +153,33 @@ __device__ __noinline__ void resolve_bins_slow(const TableDev& t, float ax_, flo
 // error margin and therefore needs tiers 2-3: nonzero / zero when DETAIL is false (the streaming
 // loops), which coordinates (bit 0/1/2 = theta_h / theta_d / phi_d) when DETAIL is true (the redo).
 // kc[] receives the candidate edges the slow tiers start from.
-//
-// Per-component tail: candidate edges from the scaled angles, and -- once the exact-edge comparisons
-// dh / dd / dp are formed -- bins and certainty.
-__device__ __forceinline__ void bins_candidates(const TableDev& t, float tq, float tdv, float tpv, int& kh, int& kd, int& kp) {
-    kh = min(__float2int_rn(t.theta_h_sqrt ? sqrt_approx(tq) : tq), t.nh);
-    kd = min(__float2int_rn(tdv), t.nd);
-    kp = min(__float2int_rn(tpv), t.np);
+template <bool DETAIL = false>
+__device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemView& v, float ax, float ay,
+                                                  float az, float bx, float by, float bz, const HalfDiff& h,
+                                                  unsigned& unc, int kc[3]) {
+    constexpr float EPS_H = 2e-6f, EPS_D = 2e-6f, EPS_P = 1.5e-6f;  // error budgets: DESIGN.md §3
+    // candidates
+    // theta_h = acos(sz/|s|) with 1 - cos written as rho^2 / (|s| (|s| + sz)): no cancellation at the
+    // small angles where MERL's sqrt-spaced bins are 2e-4 rad wide (sz > 0 for every valid query;
+    // an invalid one may produce NaN here, which F2I turns into candidate 0)
+    const float ch = __saturatef(h.sz * h.inv_s);
+    const float th_h = fast_acos01_om(ch, h.rho2 * h.inv_s * rcp_approx(h.slen + h.sz));
+    const float tq = th_h * t.kh;
+    const int kh = min(__float2int_rn(t.theta_h_sqrt ? sqrt_approx(tq) : tq), t.nh);
+    const int kd = min(__float2int_rn(fast_acos01(h.A * h.inv_s) * t.kd), t.nd);
+    float X = fmaf(h.sz, h.A, -az * h.n2);
+    float Y = h.slen * fmaf(ay, bx, -ax * by);
+    if (Y < 0.f) { X = -X; Y = -Y; }
+    const int kp = min(__float2int_rn(fast_atan2_pos(Y, X) * t.kp), t.np);
     MERL_CHECK(kh >= 0 && kh <= t.nh && kd >= 0 && kd <= t.nd && kp >= 0 && kp <= t.np);
-}
-template <bool DETAIL>
-__device__ __forceinline__ unsigned bins_decide(const TableDev& t, int kh, int kd, int kp, float dh, float dd, float dp,
-                                                float rho2, float n2, float mp, float X, float Y, Bins& b) {
-    constexpr float EPS_H = 2e-6f, EPS_D = 2e-6f;  // error budgets: DESIGN.md §3
+    // one exact-edge comparison per coordinate
+    const float eh = v.thr_h[kh], ed = v.thr_d[kd];
+    const float2 ep = v.dir_p[kp];
+    const float sz2 = h.sz * h.sz;
+    const float dh = fmaf(-eh, sz2, h.rho2);           // >= 0  <=>  theta_h >= edge kh
+    const float dd = fmaf(ed, h.n2, -h.A * fabsf(h.A)); // >= 0  <=>  theta_d >= edge kd
+    const float dp = fmaf(ep.x, Y, -ep.y * X);         // >= 0  <=>  phi_d   >= edge kp
+    Bins b;
     b.ih = max(min(kh - 1 + (dh >= 0.f), t.nh - 1), 0);  // max(): NaN inputs must not index out of range
     b.id = max(min(kd - 1 + (dd >= 0.f), t.nd - 1), 0);
     b.ip = max(min(kp - 1 + (dp >= 0.f), t.np - 1), 0);
@@ -228,82 +190,22 @@ __device__ __forceinline__ unsigned bins_decide(const TableDev& t, int kh, int k
     // guards are needed: the edge tables hold 0 / +inf (theta_h) and 4 / -4 (theta_d) there, which
     // puts |d| far outside the margin, and the clamp above makes the bin independent of d.
     // fminf drops NaN operands, so non-finite inputs are caught by the test on n2 instead.
-    const float slack_h = fmaf(-EPS_H, rho2, fabsf(dh));
-    const float slack_d = fmaf(-EPS_D, n2, fabsf(dd));
+    const float mp = EPS_P * (h.n2 + h.slen);
+    const float slack_h = fmaf(-EPS_H, h.rho2, fabsf(dh));
+    const float slack_d = fmaf(-EPS_D, h.n2, fabsf(dd));
     const float slack_p = fabsf(dp) - mp;
     const float slack_c = fmaf(-4.f * (float)t.np, mp, fabsf(X) + Y);
-    const bool finite = n2 < __int_as_float(0x7f800000);
+    const bool finite = h.n2 < __int_as_float(0x7f800000);
     if (DETAIL) {   // which coordinate(s): only the slow tiers need to know
         const unsigned all = finite ? 0u : 7u;
-        return all | (unsigned)!(slack_h > 0.f) | ((unsigned)!(slack_d > 0.f) << 1) |
-               ((unsigned)(!(slack_p > 0.f) | !(slack_c > 0.f)) << 2);
+        unc = all | (unsigned)!(slack_h > 0.f) | ((unsigned)!(slack_d > 0.f) << 1) |
+              ((unsigned)(!(slack_p > 0.f) | !(slack_c > 0.f)) << 2);
+    } else {
+        const float slack = fminf(fminf(slack_h, slack_d), fminf(slack_p, slack_c));
+        unc = (unsigned)(!(slack > 0.f) | !finite);
     }
-    const float slack = fminf(fminf(slack_h, slack_d), fminf(slack_p, slack_c));
-    return (unsigned)(!(slack > 0.f) | !finite);
-}
-
-__device__ __forceinline__ void fold_xy(float& X, float& Y) {
-    if (Y < 0.f) { X = -X; Y = -Y; }
-}
-__device__ __forceinline__ void fold_xy(float2& X, float2& Y) { fold_xy(X.x, Y.x); fold_xy(X.y, Y.y); }
-
-// The multiply/add backbone, for one query or a pair: scaled candidate angles, the folded (X, Y) of
-// phi_d, and the operands of the three exact-edge comparisons.
-template <class T> struct Tier1 { T tq, tdv, tpv, X, Y, nsz2, nAA, mp; };
-template <class T>
-__device__ __forceinline__ Tier1<T> tier1_backbone(const TableDev& t, T ax, T ay, T az, T bx, T by, const HalfDiffT<T>& h) {
-    constexpr float EPS_P = 1.5e-6f;
-    Tier1<T> r;
-    // theta_h = acos(sz/|s|) with 1 - cos written as rho^2 / (|s| (|s| + sz)): no cancellation at the
-    // small angles where MERL's sqrt-spaced bins are 2e-4 rad wide (sz > 0 for every valid query;
-    // an invalid one may produce NaN here, which F2I turns into candidate 0)
-    const T ch = p_mul_sat(h.sz, h.inv_s);
-    const T th_h = fast_acos01_om_t(ch, p_mul(p_mul(h.rho2, h.inv_s), p_rcp(p_add(h.slen, h.sz))));
-    r.tq = p_mul(th_h, p_set<T>(t.kh));
-    r.tdv = p_mul(fast_acos01_t(p_mul_sat(h.A, h.inv_s)), p_set<T>(t.kd));
-    r.X = p_fma(h.sz, h.A, p_mul(p_neg(az), h.n2));
-    r.Y = p_mul(h.slen, p_fma(ay, bx, p_mul(p_neg(ax), by)));
-    fold_xy(r.X, r.Y);
-    r.tpv = p_mul(fast_atan2_pos_t(r.Y, r.X), p_set<T>(t.kp));
-    r.nsz2 = p_mul(p_neg(h.sz), h.sz);          // -(sz^2)
-    r.nAA = p_mul(p_neg(h.A), p_abs(h.A));      // -A |A|
-    r.mp = p_mul(p_set<T>(EPS_P), p_add(h.n2, h.slen));
-    return r;
-}
-
-template <bool DETAIL = false>
-__device__ __forceinline__ Bins compute_bins_fast(const TableDev& t, const SmemView& v, float ax, float ay,
-                                                  float az, float bx, float by, float bz, const HalfDiff& h,
-                                                  unsigned& unc, int kc[3]) {
-    const Tier1<float> r = tier1_backbone<float>(t, ax, ay, az, bx, by, h);
-    int kh, kd, kp;
-    bins_candidates(t, r.tq, r.tdv, r.tpv, kh, kd, kp);
-    // one exact-edge comparison per coordinate
-    const float eh = v.thr_h[kh], ed = v.thr_d[kd];
-    const float2 ep = v.dir_p[kp];
-    const float dh = p_fma(eh, r.nsz2, h.rho2);                       // >= 0  <=>  theta_h >= edge kh
-    const float dd = p_fma(ed, h.n2, r.nAA);                          // >= 0  <=>  theta_d >= edge kd
-    const float dp = p_fma(ep.x, r.Y, p_mul(p_neg(ep.y), r.X));       // >= 0  <=>  phi_d   >= edge kp
-    Bins b;
-    unc = bins_decide<DETAIL>(t, kh, kd, kp, dh, dd, dp, h.rho2, h.n2, r.mp, r.X, r.Y, b);
     kc[0] = kh; kc[1] = kd; kc[2] = kp;
     return b;
-}
-// The same for a pair of queries (streaming loops only: no DETAIL, no candidates out).
-__device__ __forceinline__ void compute_bins_fast2(const TableDev& t, const SmemView& v, float2 ax, float2 ay, float2 az,
-                                                   float2 bx, float2 by, const HalfDiffT<float2>& h, unsigned unc[2],
-                                                   Bins b[2]) {
-    const Tier1<float2> r = tier1_backbone<float2>(t, ax, ay, az, bx, by, h);
-    int kh[2], kd[2], kp[2];
-    bins_candidates(t, r.tq.x, r.tdv.x, r.tpv.x, kh[0], kd[0], kp[0]);
-    bins_candidates(t, r.tq.y, r.tdv.y, r.tpv.y, kh[1], kd[1], kp[1]);
-    const float2 eh = make_float2(v.thr_h[kh[0]], v.thr_h[kh[1]]), ed = make_float2(v.thr_d[kd[0]], v.thr_d[kd[1]]);
-    const float2 e0 = v.dir_p[kp[0]], e1 = v.dir_p[kp[1]];
-    const float2 dh = p_fma(eh, r.nsz2, h.rho2);
-    const float2 dd = p_fma(ed, h.n2, r.nAA);
-    const float2 dp = p_fma(make_float2(e0.x, e1.x), r.Y, p_mul(p_neg(make_float2(e0.y, e1.y)), r.X));
-    unc[0] = bins_decide<false>(t, kh[0], kd[0], kp[0], dh.x, dd.x, dp.x, h.rho2.x, h.n2.x, r.mp.x, r.X.x, r.Y.x, b[0]);
-    unc[1] = bins_decide<false>(t, kh[1], kd[1], kp[1], dh.y, dd.y, dp.y, h.rho2.y, h.n2.y, r.mp.y, r.X.y, r.Y.y, b[1]);
 }
 
 // All three tiers inline: the exact bins of one query.  Used by the redo path of the streaming

@@ -209,28 +209,12 @@ __global__ void __launch_bounds__(kThreadsPerCta, MINB) stream_kernel(const Tabl
 
 // pdf of the two-lobe sampler given the theta_h bin (row A5; oracle: eval_pdf_one).  Branch-free:
 // the density is read for every lane (clamped slice index) and selected.
-template <class T>
-__device__ __forceinline__ T pdf_both_lobes(const TableDev& t, T dens, T bz, const HalfDiffT<T>& h) {
-    const T p = p_mul(p_mul(p_set<T>(1.f - t.spec_weight), bz), p_set<T>(0.318309886f));
-    return p_fma(p_mul(p_set<T>(t.spec_weight), dens), p_mul(h.slen, p_rcp(h.A)), p);
-}
-__device__ __forceinline__ int pdf_slice(const TableDev& t, float az) {
-    return max(min((int)__fmul_rn(az, (float)t.ni), t.ni - 1), 0);
-}
-__device__ __forceinline__ float pdf_cosine_only(const TableDev& t, float bz) {
-    return __fmul_rn(__fmul_rn(1.f - t.spec_weight, bz), 0.318309886f);
-}
 __device__ __forceinline__ float pdf_from_bins(const TableDev& t, const SmemView& v, float az, float bz,
                                                const HalfDiff& h, int ih) {
-    const float ps = pdf_both_lobes<float>(t, v.dens[pdf_slice(t, az) * t.nh + ih], bz, h);
-    return h.A > 0.f ? ps : pdf_cosine_only(t, bz);
-}
-// the same for a pair of queries (bit-identical per component)
-__device__ __forceinline__ float2 pdf_from_bins2(const TableDev& t, const SmemView& v, float2 az, float2 bz,
-                                                 const HalfDiffT<float2>& h, int ih0, int ih1) {
-    const float2 dens = make_float2(v.dens[pdf_slice(t, az.x) * t.nh + ih0], v.dens[pdf_slice(t, az.y) * t.nh + ih1]);
-    const float2 ps = pdf_both_lobes<float2>(t, dens, bz, h);
-    return make_float2(h.A.x > 0.f ? ps.x : pdf_cosine_only(t, bz.x), h.A.y > 0.f ? ps.y : pdf_cosine_only(t, bz.y));
+    const int j = max(min((int)(az * (float)t.ni), t.ni - 1), 0);
+    const float p = (1.f - t.spec_weight) * bz * 0.318309886f;
+    const float ps = fmaf(t.spec_weight * v.dens[j * t.nh + ih], h.slen * rcp_approx(h.A), p);
+    return h.A > 0.f ? ps : p;
 }
 __device__ __forceinline__ int flat_index(const TableDev& t, const Bins& b) {
     MERL_CHECK(b.ih >= 0 && b.ih < t.nh && b.id >= 0 && b.id < t.nd && b.ip >= 0 && b.ip < t.np);
@@ -310,46 +294,18 @@ struct QueryOp {
         Pack<VEC> pdf;
         bool valid[VEC];
         unsigned uncmask = 0;
-#ifndef MERL_PACKED2
-#define MERL_PACKED2 1
-#endif
-        if constexpr (MERL_PACKED2 && VEC % 2 == 0) {
-            // two queries per packed fp32x2 instruction (merl_device.cuh): the lane's queries go through in pairs
 #pragma unroll
-            for (int q = 0; q < VEC; q += 2) {
-                valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
-                valid[q + 1] = ((act >> (q + 1)) & 1u) && az.v[q + 1] > 0.f && bz.v[q + 1] > 0.f;
-                const float2 ax2 = make_float2(ax.v[q], ax.v[q + 1]), ay2 = make_float2(ay.v[q], ay.v[q + 1]),
-                             az2 = make_float2(az.v[q], az.v[q + 1]), bx2 = make_float2(bx.v[q], bx.v[q + 1]),
-                             by2 = make_float2(by.v[q], by.v[q + 1]), bz2 = make_float2(bz.v[q], bz.v[q + 1]);
-                const HalfDiffT<float2> h = half_diff_setup(ax2, ay2, az2, bx2, by2, bz2);
-                unsigned unc[2];
-                Bins b[2];
-                compute_bins_fast2(t, v, ax2, ay2, az2, bx2, by2, h, unc, b);
-                uncmask |= (unsigned)((unc[0] != 0u) & valid[q]) << q;
-                uncmask |= (unsigned)((unc[1] != 0u) & valid[q + 1]) << (q + 1);
-                idx[q] = flat_index(t, b[0]);
-                idx[q + 1] = flat_index(t, b[1]);
-                if (kPdf) {
-                    const float2 pq = pdf_from_bins2(t, v, az2, bz2, h, b[0].ih, b[1].ih);
-                    pdf.v[q] = valid[q] ? pq.x : 0.f;
-                    pdf.v[q + 1] = valid[q + 1] ? pq.y : 0.f;
-                }
-            }
-        } else {
-#pragma unroll
-            for (int q = 0; q < VEC; ++q) {
-                valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
-                const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
-                unsigned unc;
-                int kc[3];
-                const Bins b = compute_bins_fast(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h, unc, kc);
-                uncmask |= (unsigned)((unc != 0u) & valid[q]) << q;
-                idx[q] = flat_index(t, b);
-                if (kPdf) {
-                    const float pq = pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih);
-                    pdf.v[q] = valid[q] ? pq : 0.f;
-                }
+        for (int q = 0; q < VEC; ++q) {
+            valid[q] = ((act >> q) & 1u) && az.v[q] > 0.f && bz.v[q] > 0.f;
+            const HalfDiff h = half_diff_setup(ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q]);
+            unsigned unc;
+            int kc[3];
+            const Bins b = compute_bins_fast(t, v, ax.v[q], ay.v[q], az.v[q], bx.v[q], by.v[q], bz.v[q], h, unc, kc);
+            uncmask |= (unsigned)((unc != 0u) & valid[q]) << q;
+            idx[q] = flat_index(t, b);
+            if (kPdf) {
+                const float pq = pdf_from_bins(t, v, az.v[q], bz.v[q], h, b.ih);
+                pdf.v[q] = valid[q] ? pq : 0.f;
             }
         }
         if (kEval) {
