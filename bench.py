@@ -634,6 +634,9 @@ def render_legs(plug, world, rank, local, comm, timed, ntab):
 
     def leg(name, sc, w, h, spp, depth, reps):
         rng = RD.spp_share(spp, world, rank)
+        emu = int(os.environ.get("RD_EMULATE_WORLD", "0"))   # diagnostics: one GPU doing rank 0's share of an emu-GPU render
+        if emu > 1 and world == 1:
+            rng = RD.spp_share(spp, emu, 0)
         pb = D.PeerBuffer(comm, w * h * 4, "peer") if comm is not None else None
         film = pb.tensor((h, w, 4)) if pb is not None else torch.zeros(h, w, 4, device=dev)
 
@@ -644,7 +647,34 @@ def render_legs(plug, world, rank, local, comm, timed, ntab):
                 pb.allreduce_()
         ms, _ = timed(step, reps, 2)
         ms /= reps
+        per_rank = None
+        if comm is not None:
+            # each rank's own render time, no exchange and no barrier in the loop: is the frame time the slowest
+            # rank's render, or the waiting at the exchange?
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                film.zero_()
+                RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=rng, film=film)
+            e1.record()
+            torch.cuda.synchronize()
+            t_default = e0.elapsed_time(e1) / reps
+            e0.record()
+            for _ in range(reps):       # the same in 8 Mi-path passes (CUDA-graph replay path of merl_render)
+                film.zero_()
+                RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=rng, film=film, wavefront=1 << 23)
+            e1.record()
+            torch.cuda.synchronize()
+            mine = torch.tensor([t_default, e0.elapsed_time(e1) / reps], device=dev, dtype=torch.float64)
+            allr = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            per_rank = {"default_pass_size": [round(float(x[0]), 4) for x in allr],
+                        "passes_of_8Mi": [round(float(x[1]), 4) for x in allr],
+                        "free_gib": round(torch.cuda.mem_get_info()[0] / 2**30, 1)}
         out[name] = {"width": w, "height": h, "spp": spp, "max_depth": depth, "ms": ms,
+                     "render_only_ms_per_rank": per_rank,
                      "spp_mpix_per_s": spp * w * h / 1e6 / (ms * 1e-3),
                      "mean_radiance": [float(x) for x in film[..., :3].mean(dim=(0, 1))],
                      "sample_share_min_max": [float(film[..., 3].min()), float(film[..., 3].max())],

@@ -38,12 +38,22 @@ def main():
     if emu > 1 and world == 1:
         rng = RD.spp_share(spp, emu, 0)
     wf = int(os.environ.get("MERL_WAVEFRONT", "0"))   # paths per pass; 0 = the library's default
-    film = torch.zeros(h, w, 4, device=dev)
+    pb = None
+    if comm is not None and os.environ.get("RD_FILM_PEER", "0") == "1":   # as bench.py: the film lives in an exchange buffer
+        pb = D.PeerBuffer(comm, w * h * 4, "peer")
+        film = pb.tensor((h, w, 4))
+    else:
+        film = torch.zeros(h, w, 4, device=dev)
+    if rank == 0:
+        fr, tot = torch.cuda.mem_get_info()
+        print(f"# free device memory before the first render: {fr / 2**30:.1f} of {tot / 2**30:.1f} GiB", file=sys.stderr)
 
     def step():
         film.zero_()
         RD.render(sc, w, h, spp, max_depth=depth, seed=1, spp_range=rng, film=film, wavefront=wf)
-        if comm is not None:
+        if pb is not None:
+            pb.allreduce_()
+        elif comm is not None:
             comm.allreduce_sum_(film)
 
     for _ in range(2):
