@@ -1749,12 +1749,19 @@ static int merl_render_impl(const merl_table_t* const* tables, int ntables, cons
     // six launches at their latency floor each, so fewer, fatter passes are faster -- config 5 (268 M paths):
     // 4873 / 5515 / 5850 / 6019 spp Mpix/s at 8 / 16 / 32 / 64 Mi paths per pass (profiles/r02_render_wavefront.txt).
     // The default stays below a quarter of the device memory that is free right now.
+    // (decided once per device and process: cudaMemGetInfo costs ~50 us, a tenth of a small frame)
     int64_t cap = p->wavefront;
     if (cap <= 0) {
-        cap = (int64_t)1 << 26;
-        size_t free_b = 0, total_b = 0;
-        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); free_b = (size_t)8 << 30; }
-        while (cap > (1 << 20) && (size_t)cap * 264 > free_b / 4) cap >>= 1;
+        static std::atomic<int64_t> decided[64];
+        const int di = t0->device & 63;
+        cap = decided[di].load();
+        if (cap == 0) {
+            cap = (int64_t)1 << 26;
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); free_b = (size_t)8 << 30; }
+            while (cap > (1 << 20) && (size_t)cap * 264 > free_b / 4) cap >>= 1;
+            decided[di].store(cap);
+        }
     }
     if (cap > total) cap = total;
     cap = (cap + 255) & ~(int64_t)255;
@@ -1769,12 +1776,24 @@ static int merl_render_impl(const merl_table_t* const* tables, int ntables, cons
 
     // one stream-ordered workspace: path state, stage buffers, sort scratch, scene
     const size_t nf4 = 6, ni = 4;   // path state: six float4 and four int arrays
-    size_t bytes = cap * (nf4 * 16 + ni * 4) + cap * 16 * 9 + 512;
-    bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(4 * ntables + 4) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
-    bytes += (size_t)cap * 4 * 2 + 512 + 256 + (size_t)kMaxClusters * 32 + 256 + 256;   // live lists, their counters, clusters, pass info
     char* ws = nullptr;
-    if (cudaMemPool_t pool = render_pool(t0->device)) CUDA_TRY(cudaMallocFromPoolAsync((void**)&ws, bytes, pool, s));
-    else CUDA_TRY(cudaMallocAsync(&ws, bytes, s));
+    for (;;) {
+        size_t bytes = cap * (nf4 * 16 + ni * 4) + cap * 16 * 9 + 512;
+        bytes += (size_t)nspheres * (16 + 4) + 256 + (size_t)(4 * ntables + 4) * 4 + 256 + sizeof(TableDev) * ntables + 256 + 64;
+        bytes += (size_t)cap * 4 * 2 + 512 + 256 + (size_t)kMaxClusters * 32 + 256 + 256;   // live lists, their counters, clusters, pass info
+        cudaMemPool_t pool = render_pool(t0->device);
+        const cudaError_t e = pool ? cudaMallocFromPoolAsync((void**)&ws, bytes, pool, s) : cudaMallocAsync(&ws, bytes, s);
+        if (e == cudaSuccess) break;
+        cudaGetLastError();
+        // the default pass size was chosen from the memory free at the first call: if the device has filled up
+        // since, halve it (an explicit p->wavefront is the caller's decision and fails loudly instead)
+        if (e == cudaErrorMemoryAllocation && p->wavefront <= 0 && own_world == 1 && cap > (1 << 20)) {
+            cap = ((cap / 2) + 255) & ~(int64_t)255;
+            continue;
+        }
+        return fail(e == cudaErrorMemoryAllocation ? MERL_ERR_NOMEM : MERL_ERR_CUDA, "render workspace of %zu bytes: %s", bytes,
+                    cudaGetErrorString(e));
+    }
     char* cur = ws;
     auto take = [&](size_t b) { char* r = cur; cur += (b + 255) & ~(size_t)255; return r; };
     float4* f4 = reinterpret_cast<float4*>(take(cap * 16 * 9));
