@@ -127,3 +127,31 @@ def test_corrupt_file_header_is_an_error_not_an_exception(built_lib, tmp_path):
     short.write_bytes(np.array([64, 96, 192], dtype=np.int32).tobytes() + b"\0" * 1000)
     rc = built_lib.merl_table_create_from_file(str(short).encode(), C.byref(p), 0, C.byref(h))
     assert rc == -2 and b"needs" in built_lib.merl_last_error()
+
+
+def test_python_constants_match_header():
+    """The flag / transport / error values the ctypes binding hard-codes are the header's."""
+    import re
+    from mitsuba_customization_b200 import _cabi
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "merl_b200.h")).read()
+
+    def define(name):
+        m = re.search(r"#define\s+%s\s+(-?\d+)u?\b" % name, hdr)
+        assert m, f"{name} not #defined in merl_b200.h"
+        return int(m.group(1))
+    assert define("MERL_BWD_WARP_AGGREGATE") == _cabi.BWD_WARP_AGGREGATE
+    assert define("MERL_BWD_DEFER_MASK") == _cabi.BWD_DEFER_MASK
+    assert define("MERL_BWD_CTA_AGGREGATE") == _cabi.BWD_CTA_AGGREGATE
+    assert (define("MERL_XCHG_PEER"), define("MERL_XCHG_NCCL"), define("MERL_XCHG_NVLS")) == \
+        (_cabi.XCHG_PEER, _cabi.XCHG_NCCL, _cabi.XCHG_NVLS)
+    m = re.search(r"MERL_ERR_UNSUPPORTED\s*=\s*(-?\d+)", hdr)
+    assert m and int(m.group(1)) == _cabi.ERR_UNSUPPORTED
+
+
+def test_unknown_exchange_transport_is_rejected(built_lib):
+    """merl_peerbuf_create checks its arguments before touching NCCL or the device."""
+    import ctypes as C
+    from mitsuba_customization_b200 import _cabi
+    h = C.c_void_p()
+    assert _cabi.lib().merl_peerbuf_create(None, 16, _cabi.XCHG_PEER, C.byref(h)) != 0      # no communicator
+    assert b"argument" in _cabi.lib().merl_last_error().lower()
