@@ -194,6 +194,33 @@ int merl_sample_host(const merl_table_t* t, const float* wix, const float* wiy, 
                      const float* u1, const float* u2x, const float* u2y, int64_t n, float* wox,
                      float* woy, float* woz, float* pdf, float* wr, float* wg, float* wb, uint32_t* lobe);
 
+/* ---- the same eval+pdf on host buffers, for callers that must not allocate --------------------
+ * No counterpart in the reference: this entry point exists only because of how this library is
+ * hosted.  merl_eval_pdf_host cudaMallocs its device staging buffers on first use and regrows them
+ * for a larger batch.  That is wrong for three kinds of caller: a renderer that has already given
+ * the whole device to its own pool (Dr.Jit's or torch's caching allocator, a scene of a hundred
+ * tables), where a late cudaMalloc fails or forces the pool to shrink; a frame or optimiser loop
+ * that cannot afford the device-wide synchronisation that cudaMalloc and cudaFree imply; and a
+ * scalar-variant plugin queried from many worker threads, where the first query on each new table
+ * would stall all of them while buffers are made.
+ * merl_eval_pdf_host_static stages through a fixed array that is part of the library image instead
+ * (40 bytes per query, MERL_STATIC_STAGE_MAX_QUERIES queries = 2.5 MiB, resident on every GPU the
+ * library is loaded on until the process exits).  It calls no cudaMalloc / cudaFree / pool or
+ * stream-creation routine: copy in on `stream`, one eval+pdf launch (two when n is not a multiple
+ * of 4), copy out, cudaStreamSynchronize(stream).  Same arguments, results (bit for bit) and
+ * errors as merl_eval_pdf_host, plus:
+ *   - n > MERL_STATIC_STAGE_MAX_QUERIES is refused with MERL_ERR_ARG; split the batch.
+ *   - The first call on each device looks up the array's device address and the kernel's occupancy
+ *     figure (host-side bookkeeping only).  Make that first call outside any stream capture.
+ *   - All calls on a device share the one array, which keeps the previous call's data; the entry
+ *     point overwrites every element it reads, so nothing leaks between calls.  Calls from one
+ *     process are serialised by a lock held until the copy-back has finished.  Work that would
+ *     touch the array concurrently on the GPU by any other route would race. */
+#define MERL_STATIC_STAGE_MAX_QUERIES 65536
+int merl_eval_pdf_host_static(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                              const float* wox, const float* woy, const float* woz, int64_t n, float* r,
+                              float* g, float* b, float* pdf, merl_stream_t stream);
+
 /* ---- wavefront path tracer harness (BASELINE configs 2 and 5) ------------
  * The callers either side of the BSDF stage, headless: spheres under a constant environment map,
  * pinhole camera, path integrator with emitter sampling + BSDF sampling combined by the power

@@ -21,6 +21,7 @@ SYMBOLS = [
     "merl_file_report", "merl_table_save_packed", "merl_table_create_from_packed",
     "merl_bins", "merl_eval", "merl_pdf", "merl_eval_pdf", "merl_sample", "merl_backward",
     "merl_eval_pdf_aos", "merl_sample_aos", "merl_eval_pdf_host", "merl_sample_host",
+    "merl_eval_pdf_host_static",
     "merl_render", "merl_set_render_graphs",
     "merl_comm_unique_id", "merl_comm_create", "merl_comm_destroy", "merl_allreduce_sum_f32",
     "merl_grad_apply_mask",
@@ -33,6 +34,7 @@ BWD_DEFER_MASK = 2
 BWD_CTA_AGGREGATE = 4
 XCHG_PEER, XCHG_NCCL, XCHG_NVLS = 0, 1, 2
 ERR_UNSUPPORTED = -5
+STATIC_STAGE_MAX_QUERIES = 65536
 
 
 class MerlError(RuntimeError):
@@ -111,6 +113,7 @@ def lib():
         L.merl_sample_aos.argtypes = [vp, vp, vp, i64, vp, vp, vp]
         L.merl_eval_pdf_host.argtypes = [vp] + [vp] * 6 + [i64] + [vp] * 4
         L.merl_sample_host.argtypes = [vp] + [vp] * 6 + [i64] + [vp] * 8
+        L.merl_eval_pdf_host_static.argtypes = [vp] + [vp] * 6 + [i64] + [vp] * 4 + [vp]
         L.merl_set_sample_search.argtypes = [i32]
         L.merl_set_render_graphs.argtypes = [i32]
         L.merl_render.argtypes = [vp, i32, vp, i32, vp, vp, vp, vp]

@@ -1119,6 +1119,96 @@ extern "C" int merl_sample_host(const merl_table_t* tc, const float* wix, const 
 }
 
 // ------------------------------------------------------------------------------------------
+// merl_eval_pdf_host_static: the host-buffer eval+pdf without any allocation.
+//
+// merl_eval_pdf_host above stages the caller's host arrays through device buffers that it
+// cudaMallocs on first use (and regrows for a larger call).  Some hosts of this library must not
+// trigger that: a renderer whose own pool (Dr.Jit's allocator, a torch caching allocator, a 100-table
+// scene) has already claimed the device memory, so a late cudaMalloc fails or evicts; a frame loop
+// that cannot take the device-wide synchronisation cudaMalloc/cudaFree imply; a scalar-variant plugin
+// called from many worker threads where the first query of each new table would stall the others.
+// For them the staging area is a fixed array in the library's own image, below.  It costs
+// kStaticStageBytes of device memory on every GPU this library is loaded on, from load until exit,
+// whether or not the entry point is ever called.
+//
+// g_static_stage is a HOST-SIDE STAND-IN in host code: its address there is not a device address.
+// static_stage_for_current_device() resolves the real one with cudaGetSymbolAddress, once per device,
+// with that device current, and only that pointer is handed to copies and kernels.
+// ------------------------------------------------------------------------------------------
+static constexpr int64_t kStaticStageQueries = MERL_STATIC_STAGE_MAX_QUERIES;
+static constexpr int kStaticStageArrays = 10;   // wi.xyz, wo.xyz in; r, g, b, pdf out
+static constexpr size_t kStaticStageBytes = sizeof(float) * kStaticStageArrays * kStaticStageQueries;
+static __device__ __align__(256) float g_static_stage[kStaticStageArrays * kStaticStageQueries];
+static_assert(kStaticStageBytes <= (4u << 20), "the resident staging array is meant to stay small");
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu[kStaticMaxDevices];         // one call at a time per device: they share the array
+float* g_static_ptr[kStaticMaxDevices] = {};      // device address of g_static_stage, per device
+std::mutex g_static_setup_mu;
+
+// The caller has made `device` current.  First call per device: look the symbol up (no allocation;
+// the array was placed when the module was loaded onto that device).
+int static_stage_for_current_device(int device, float** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return fail(MERL_ERR_UNSUPPORTED, "device %d: static staging supports devices 0..%d", device, kStaticMaxDevices - 1);
+    std::lock_guard<std::mutex> lk(g_static_setup_mu);
+    if (!g_static_ptr[device]) {
+        float* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_stage);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(MERL_ERR_CUDA, "cudaGetSymbolAddress(static staging array) on device %d: %s", device, cudaGetErrorString(e));
+        }
+        g_static_ptr[device] = p;
+    }
+    *out = g_static_ptr[device];
+    return MERL_OK;
+}
+}  // namespace
+
+static int merl_eval_pdf_host_static_impl(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                                         const float* wox, const float* woy, const float* woz, int64_t n, float* r,
+                                         float* g, float* b, float* pdf, cudaStream_t s) {
+    MERL_RANGE("merl_eval_pdf_host_static");
+    int rc = check_query_args(t, wix, wiy, wiz, wox, woy, woz, n);
+    if (rc) return rc;
+    if (n > kStaticStageQueries)
+        return fail(MERL_ERR_ARG, "merl_eval_pdf_host_static: n = %lld exceeds MERL_STATIC_STAGE_MAX_QUERIES = %lld "
+                    "(split the batch, or use merl_eval_pdf_host, which allocates)", (long long)n, (long long)kStaticStageQueries);
+    if (n > 0 && (!r || !g || !b || !pdf)) return fail(MERL_ERR_ARG, "output pointer is NULL");
+    if (n == 0) return MERL_OK;
+    DeviceGuard gd(t->device);
+    float* stage = nullptr;
+    if ((rc = static_stage_for_current_device(t->device, &stage))) return rc;
+    // The array is shared by every call on this device and still holds the previous call's queries and
+    // results.  Nothing in it has to start at zero: elements [0, n) of the six input arrays are
+    // overwritten by the copies below before the kernel reads them, the kernel writes elements [0, n)
+    // of the four output arrays for every lane (inactive and below-horizon lanes store zeros), and
+    // nothing past n is read or copied back.
+    std::lock_guard<std::mutex> lk(g_static_mu[t->device]);
+    const int64_t C = kStaticStageQueries;
+    const float* src[6] = {wix, wiy, wiz, wox, woy, woz};
+    float* dst[4] = {r, g, b, pdf};
+    for (int a = 0; a < 6; ++a)
+        CUDA_TRY(cudaMemcpyAsync(stage + a * C, src[a], sizeof(float) * n, cudaMemcpyHostToDevice, s));
+    float* dq = stage + 6 * C;
+    const QueryIn in{stage, stage + C, stage + 2 * C, stage + 3 * C, stage + 4 * C, stage + 5 * C, nullptr};
+    const QueryOut out{dq, dq + C, dq + 2 * C, dq + 3 * C, nullptr};
+    if ((rc = run_query_mode<MODE_EVAL_PDF>(t, in, n, out, s))) return rc;
+    for (int a = 0; a < 4; ++a)
+        CUDA_TRY(cudaMemcpyAsync(dst[a], dq + a * C, sizeof(float) * n, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));   // results are in the host buffers on return; the lock covers the GPU work
+    return MERL_OK;
+}
+extern "C" int merl_eval_pdf_host_static(const merl_table_t* t, const float* wix, const float* wiy, const float* wiz,
+                                         const float* wox, const float* woy, const float* woz, int64_t n, float* r,
+                                         float* g, float* b, float* pdf, merl_stream_t stream) {
+    return guarded("merl_eval_pdf_host_static", [&]() -> int {
+        return merl_eval_pdf_host_static_impl(t, wix, wiy, wiz, wox, woy, woz, n, r, g, b, pdf, (cudaStream_t)stream);
+    });
+}
+
+// ------------------------------------------------------------------------------------------
 // multi-GPU exchange step: NCCL bound at run time (no link-time dependency)
 // ------------------------------------------------------------------------------------------
 namespace {

@@ -144,6 +144,7 @@ def test_python_constants_match_header():
     assert define("MERL_BWD_CTA_AGGREGATE") == _cabi.BWD_CTA_AGGREGATE
     assert (define("MERL_XCHG_PEER"), define("MERL_XCHG_NCCL"), define("MERL_XCHG_NVLS")) == \
         (_cabi.XCHG_PEER, _cabi.XCHG_NCCL, _cabi.XCHG_NVLS)
+    assert define("MERL_STATIC_STAGE_MAX_QUERIES") == _cabi.STATIC_STAGE_MAX_QUERIES
     m = re.search(r"MERL_ERR_UNSUPPORTED\s*=\s*(-?\d+)", hdr)
     assert m and int(m.group(1)) == _cabi.ERR_UNSUPPORTED
 
