@@ -166,6 +166,9 @@ public:
             dr::resize(wi.x(), n); dr::resize(wi.y(), n); dr::resize(wi.z(), n);
             dr::resize(u1, n); dr::resize(u2.x(), n); dr::resize(u2.y(), n); dr::resize(active, n);
             dr::eval(wi, u1, u2, active);                 // materialise: the external call breaks the megakernel
+            // llvm_*: dr::eval() only queues the kernels on Dr.Jit's thread pool; the host-buffer entry point
+            // reads the packets' memory right away, so wait for them (CUDA variants are ordered by the stream)
+            if constexpr (dr::is_llvm_v<Float>) dr::sync_thread();
             Float ox = dr::empty<Float>(n), oy = dr::empty<Float>(n), oz = dr::empty<Float>(n),
                   p = dr::empty<Float>(n), wr = dr::empty<Float>(n), wg = dr::empty<Float>(n),
                   wb = dr::empty<Float>(n);
@@ -305,6 +308,9 @@ protected:
         dr::resize(wo.x(), n); dr::resize(wo.y(), n); dr::resize(wo.z(), n);
         dr::resize(active, n);
         dr::eval(wi, wo, active);
+        // llvm_*: evaluation is asynchronous on Dr.Jit's thread pool and the packets are handed to the library
+        // as plain host memory next; CUDA variants need no wait (same stream as the library's launches)
+        if constexpr (dr::is_llvm_v<Float>) dr::sync_thread();
         return n;
     }
     // Dr.Jit CUDA masks store one byte per lane, which is what the ABI's `active` expects.

@@ -110,8 +110,19 @@ inline void mock_no_symbolic(const char* what) {
     if (jit_flag(JitFlag::Recording))
         throw std::runtime_error(std::string("drjit mock: ") + what + " of a symbolic (placeholder) variable while recording");
 }
-template <typename T> T* LLVMArray<T>::data() { mock_no_symbolic("data()"); return buf.get(); }
-template <typename T> const T* LLVMArray<T>::data() const { mock_no_symbolic("data()"); return buf.get(); }
+// Dr.Jit's LLVM backend runs dr::eval()'s kernels asynchronously on its thread pool: the host memory
+// behind data() is valid only after dr::sync_thread().  The mock computes nothing asynchronously, so it
+// models the hazard instead: eval() marks host packets as in flight, sync_thread() clears the mark, and
+// reading an LLVM array's data() in between raises.
+inline bool& mock_llvm_in_flight() { static bool f = false; return f; }
+inline int& mock_sync_thread_calls() { static int n = 0; return n; }
+inline void mock_llvm_synced(const char* what) {
+    if (mock_llvm_in_flight())
+        throw std::runtime_error(std::string("drjit mock: ") + what + " of an LLVM array after dr::eval() without dr::sync_thread(): "
+                                 "the LLVM backend may still be writing the packet");
+}
+template <typename T> T* LLVMArray<T>::data() { mock_no_symbolic("data()"); mock_llvm_synced("data()"); return buf.get(); }
+template <typename T> const T* LLVMArray<T>::data() const { mock_no_symbolic("data()"); mock_llvm_synced("data()"); return buf.get(); }
 
 template <typename T> struct is_cuda : std::false_type {};
 template <typename T> struct is_cuda<CUDAArray<T>> : std::true_type {};
@@ -168,7 +179,7 @@ template <typename A> void resize(A& a, size_t n) {
     }
 }
 // mock arrays are always materialised; while "recording" an evaluation raises, as in Dr.Jit
-template <typename... Ts> void eval(const Ts&...) { mock_no_symbolic("eval()"); }
+template <typename... Ts> void eval(const Ts&...) { mock_no_symbolic("eval()"); mock_llvm_in_flight() = true; }
 // dr::select on host packets (the llvm branch of the plugin masks its results with it)
 template <typename T> LLVMArray<T> select(const LLVMArray<bool>& m, const LLVMArray<T>& a, const LLVMArray<T>& b) {
     const size_t n = std::max(m.size(), std::max(a.size(), b.size()));
@@ -177,7 +188,11 @@ template <typename T> LLVMArray<T> select(const LLVMArray<bool>& m, const LLVMAr
         r.buf[i] = m.buf[m.size() == 1 ? 0 : i] ? a.buf[a.size() == 1 ? 0 : i] : b.buf[b.size() == 1 ? 0 : i];
     return r;
 }
-inline void sync_thread() { mock_cuda_check(cudaDeviceSynchronize(), "cudaDeviceSynchronize"); }
+inline void sync_thread() {
+    mock_cuda_check(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
+    mock_llvm_in_flight() = false;
+    ++mock_sync_thread_calls();
+}
 
 }  // namespace drjit
 

@@ -88,11 +88,15 @@ int main(int argc, char** argv) {
             }
             auto active = dr::load<dr::LLVMArray<bool>>(act.data(), n);
             const int64_t calls0 = merl_launch_count();
+            const int syncs0 = dr::mock_sync_thread_calls();
             auto [rgb, pdf] = bsdf->eval_pdf(ctx, si, wod, active);
             auto rgb_only = bsdf->eval(ctx, si, wod, active);
             auto pdf_only = bsdf->pdf(ctx, si, wod, active);
             Vector<FloatL, 2> s2(dr::load<FloatL>(u2.data(), n), dr::load<FloatL>(u2.data() + n, n));
             auto [bs, weight] = bsdf->sample(ctx, si, dr::load<FloatL>(u1.data(), n), s2, active);
+            // every virtual waits for Dr.Jit's asynchronous LLVM evaluation before handing host pointers over
+            // (the mock's data() raises otherwise; this counts the waits)
+            if (dr::mock_sync_thread_calls() - syncs0 < 4) Throw("llvm variant: fewer than one dr::sync_thread() per virtual");
             std::ofstream fl(std::string(argv[4]) + ".llvm", std::ios::binary);
             auto host = [](const FloatL& a) { std::vector<float> h(a.size()); dr::store(h.data(), a); return h; };
             for (int c = 0; c < 3; ++c) write_vec(fl, host(rgb.v[c]));
