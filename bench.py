@@ -8,7 +8,7 @@ through the C ABI) over one batch of 2^26 synthetic (wi, wo) pairs per GPU again
 synthetic MERL table.  One JSON line is printed by rank 0:
 
   value      whole-job Gquery/s with the batch resident in HBM (CUDA events, max over ranks), timed
-             over exactly K steps that follow W + `--preheat` untimed steps, i.e. in the SUSTAINED
+             over exactly K steps that follow a barrier and then W + `--preheat` untimed steps, i.e. in the SUSTAINED
              state a renderer holds the kernel in (the first ~30 ms after an idle period run 7-14 %
              faster: that burst figure is extras.eval_pdf_burst)
   e2e        the same metric through merl_eval_pdf_host with PINNED HOST buffers: every step
@@ -23,8 +23,9 @@ synthetic MERL table.  One JSON line is printed by rank 0:
              one exchange per 1 / 4 / 16 batches, BASELINE config 4, and an on-box correctness check
   extras.render         BASELINE configs 2 and 5 (spp*Mpix/s), and config 5 sharded by table
 
---impl reference times that CPU port alone (the reference's own plugins cannot be built:
-/root/reference holds no source).
+--impl reference times that CPU port alone on the SAME step (all 2^26 queries per step, --steps and
+--warmup as given; the reference's own plugins cannot be built: /root/reference holds no source,
+see DESIGN.md §7).
 """
 from __future__ import annotations
 
@@ -161,27 +162,36 @@ def run_reference(args):
     raw = synth.synthetic_table(0)
     t = O.OracleTable(raw)
     t.build_cdf()
-    n = 1 << 22  # bounded sample of the 2^26-query step
+    # one step = the GPU arm's whole step (2^log2_batch queries), walked in 2^22-query calls so that the
+    # oracle's fp64 result arrays stay at 150 MB per call instead of 2.4 GB of fresh pages per step
+    n = 1 << args.log2_batch
+    chunk = min(n, 1 << 22)
     wi, wo = synth.random_queries(n, seed=1234)
-    steps = max(1, min(args.steps, 40))
-    warm = max(1, min(args.warmup, 3))
+
+    def step():
+        for o in range(0, n, chunk):
+            t.eval_pdf(wi[:, o:o + chunk], wo[:, o:o + chunk])
+
+    steps = max(1, args.steps)
+    warm = max(0, args.warmup)
     for _ in range(warm):
-        t.eval_pdf(wi, wo)
+        step()
     t0 = time.perf_counter()
     for _ in range(steps):
-        t.eval_pdf(wi, wo)
+        step()
     dt = time.perf_counter() - t0
     v = n * steps / dt / 1e9
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "step_sample": "2^22 of the step's 2^26 queries per step (bounded CPU sample)"},
+        "config": {"workload": WORKLOAD, "queries_per_gpu_per_step": n, "table": "synthetic MERL id 0",
+                   "step_sample": f"the whole step: 2^{args.log2_batch} queries per step, in {n // chunk} calls of 2^22"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{steps} steps x 2^22 eval+pdf queries, OpenMP over all {cores} host threads of the "
-                                   "affinity mask (OMP_NUM_THREADS ignored); the reference's own plugins are absent from "
-                                   "/root/reference, so this is the CPU restatement (oracle/merl_oracle.c), not the "
-                                   "reference binary"},
+                         "sample": f"{steps} steps x 2^{args.log2_batch} eval+pdf queries (the full step), OpenMP over all "
+                                   f"{cores} host threads of the affinity mask (OMP_NUM_THREADS ignored); the reference's own "
+                                   "plugins are absent from /root/reference, so this is the CPU restatement "
+                                   "(oracle/merl_oracle.c), not the reference binary"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -287,11 +297,14 @@ def run_b200(args):
     sampler = ClockSampler(local)
 
     def timed(fn, steps, warmup):
+        # barrier FIRST, then the untimed steps, then the start event with no host round trip in between:
+        # a barrier (dist.barrier + device sync) idles the board long enough to leave its power cap, so
+        # placed after the preheat it made N >= 2 report the burst rate and N = 1 the sustained one
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         for _ in range(warmup):
             fn()
-        barrier()
         l0 = _cabi.launch_count()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
             fn()
@@ -469,7 +482,7 @@ def run_b200(args):
             roof["frac_config3_customized_2p24"] = extras["customized_2p24"]["eval_pdf_frac_of_hbm"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": W + max(0, args.preheat),
+            "warmup": W, "preheat": max(0, args.preheat),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "queries_per_gpu_per_step": n, "table": "synthetic MERL id 0",

@@ -14,9 +14,12 @@ def _run(*args, timeout=600):
 
 
 def test_reference_arm_prints_the_contract_line(built_lib):
-    r = _run("--impl", "reference", "--steps", "1", "--warmup", "1")
+    # the full step is 2^26 queries (about a second on the GPU box's host cores); a CPU test takes 2^22
+    r = _run("--impl", "reference", "--steps", "2", "--warmup", "1", "--log2-batch", "22")
     assert r.returncode == 0, r.stderr
     line = json.loads(r.stdout.strip().splitlines()[-1])
+    # --steps / --warmup are honoured as given and a step is the whole batch (same config keys as the GPU arm)
+    assert line["steps"] == 2 and line["warmup"] == 1 and line["config"]["queries_per_gpu_per_step"] == 1 << 22
     assert line["impl"] == "reference" and line["metric"] == "merl_eval_pdf_throughput" and line["unit"] == "Gquery/s"
     assert line["higher_is_better"] is True and line["value"] > 0 and line["n_gpus"] == 1
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
@@ -39,7 +42,7 @@ def test_reference_arm_ignores_torchrun_thread_cap(built_lib):
     of its affinity mask, so that the driver's ratio means the same at every N."""
     env = dict(os.environ, OMP_NUM_THREADS="1", RANK="0", WORLD_SIZE="2")
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
-                        "--warmup", "1"], capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+                        "--warmup", "1", "--log2-batch", "22"], capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
     assert r.returncode == 0, r.stderr
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0)) and line["n_gpus"] == 2
