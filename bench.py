@@ -135,6 +135,47 @@ def cpu_legs(budget_s=8.0):
         cfg1[name] = {"threads": nt, "eval_pdf_gquery_s": ve, "sample_gquery_s": vs,
                       "eval_pdf_sample_ms": m / ve / 1e6 + m / vs / 1e6}
     out["config1_2p20"] = cfg1
+    out["render"] = cpu_render_legs(t, cores)
+    return out
+
+
+def cpu_render_legs(t0, cores, budget_s=6.0):
+    """The render half of the metric on the host cores: BASELINE configs 2 and 5 through oracle/render_oracle.c
+    (the CPU statement of the algorithm merl_render runs), a bounded share of the samples, all threads."""
+    import numpy as np
+    from mitsuba_customization_b200 import render as RD, synth
+    from oracle import merl_oracle as O, render_oracle as RO
+
+    def leg(tables, sc, w, h, spp, depth, nthreads, budget):
+        O.set_threads(nthreads)
+        kw = dict(width=w, height=h, spp=spp, max_depth=depth, seed=1, cam_pos=sc.cam_pos, cam_target=sc.cam_target,
+                  cam_up=sc.cam_up, fov_x_deg=sc.fov_x_deg, env=sc.env)
+        a = time.perf_counter()
+        RO.render(tables, sc.spheres, spp_begin=0, spp_end=1, **kw)        # 1 spp: sizes the sample (and warms up)
+        per_spp = time.perf_counter() - a
+        cs = int(max(1, min(spp, budget / max(per_spp, 1e-6))))
+        a = time.perf_counter()
+        film = RO.render(tables, sc.spheres, spp_begin=0, spp_end=cs, **kw)
+        dt = time.perf_counter() - a
+        return {"spp_mpix_per_s": cs * w * h / 1e6 / dt, "threads": nthreads, "width": w, "height": h, "max_depth": depth,
+                "sample": f"{cs} of {spp} spp, {dt:.2f} s", "mean_radiance_of_sample": float(film[..., :3].mean()) * spp / cs}
+
+    out = {}
+    sc2 = RD.sphere_scene(None)
+    out["cfg2_all_threads"] = leg([t0], sc2, 512, 512, 64, 8, cores, budget_s)
+    out["cfg2_single_thread"] = leg([t0], sc2, 512, 512, 64, 8, 1, 2.0)
+    # config 5: 100 tables that are distinct in memory (35 MB of doubles each).  Synthesising 100 takes minutes on
+    # the host, so: 10 synthetic ids x 10 brightness factors, each its own array and its own CDF.
+    base = [synth.synthetic_table(k) for k in range(10)]
+    tabs = []
+    for k in range(100):
+        tk = O.OracleTable(np.ascontiguousarray(base[k % 10] * (0.55 + 0.05 * (k // 10))))
+        tk.build_cdf()
+        tabs.append(tk)
+    sc5 = RD.grid_scene([None] * 100, 10, 10)
+    out["cfg5_all_threads"] = leg(tabs, sc5, 1024, 1024, 256, 8, cores, budget_s)
+    out["cfg5_all_threads"]["tables"] = "100 distinct arrays: 10 synthetic ids x 10 brightness factors"
+    O.set_threads(cores)
     return out
 
 
@@ -508,12 +549,53 @@ def run_b200(args):
                                         "single_thread": c["config1_2p20"]["single_thread"]["eval_pdf_gquery_s"],
                                         "sample_gquery_s": c["config1_2p20"]["all_threads"]["sample_gquery_s"],
                                         "config1_2p20": c["config1_2p20"],
+                                        "render_cfg2_spp_mpix_s": c["render"]["cfg2_all_threads"]["spp_mpix_per_s"],
+                                        "render_cfg5_spp_mpix_s": c["render"]["cfg5_all_threads"]["spp_mpix_per_s"],
+                                        "render": c["render"],
                                         "process": "subprocess (bench.py --cpu-legs): the GPU arm never loads oracle/"}
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"}
+        # last key of the line, so that a tail of the output still holds the multi-GPU record
+        line["scaling_summary"] = scaling_summary(extras, world)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def scaling_summary(extras, world):
+    """A compact (< 1200 characters) digest of extras.grad_scaling / extras.render: what a reader of the last
+    1500 characters of the line needs to judge the gradient pass and the render legs."""
+    def r3(x):
+        return None if x is None else round(float(x), 4)
+    s = {"n": world}
+    g = extras.get("grad_scaling") or {}
+    if "error" in g:
+        s["grad_error"] = str(g["error"])[:120]
+    elif g:
+        s["bwd_gq_s_per_gpu"] = r3(g.get("backward_gquery_s_per_gpu_no_exchange"))
+        s["allreduce_check"] = g.get("allreduce_check", "n/a (1 GPU)")
+        tr = g.get("transports") or {}
+        best = max((t for t in tr if "weak_efficiency_vs_no_exchange_every_1" in tr[t]),
+                   key=lambda t: tr[t]["weak_efficiency_vs_no_exchange_every_1"], default=None)
+        if best:
+            b = tr[best]
+            s["grad"] = {"transport": best, "xchg_us": r3(b.get("exchange_ms", 0) * 1e3),
+                         "eff_every": [r3(b.get(f"weak_efficiency_vs_no_exchange_every_{m}")) for m in (1, 4, 16)]}
+        c4 = g.get("config4_2p26_total") or {}
+        ms = [v for k2, v in c4.items() if k2.endswith("_ms") and k2 != "scatter_only_ms"]
+        if ms:
+            s["cfg4_ms"] = r3(min(ms))
+    r = extras.get("render") or {}
+    if "error" in r:
+        s["render_error"] = str(r["error"])[:120]
+    for name in ("cfg2", "cfg5"):
+        if name in r:
+            s[name] = {"spp_mpix_s": round(r[name]["spp_mpix_per_s"], 1),
+                       "film_check": r[name].get("film_check", {}).get("verdict"),
+                       "rel_mse": r[name].get("film_check", {}).get("rel_mse_exchanged_vs_one_gpu_render")}
+    if "cfg5_by_table" in r:
+        s["cfg5_by_table_rel_mse"] = r["cfg5_by_table"].get("rel_mse_vs_replicated_same_samples")
+    return s
 
 
 def grad_legs(plug, si, wo, n, world, rank, local, comm, timed, gen, k):
@@ -660,6 +742,23 @@ def render_legs(plug, world, rank, local, comm, timed, ntab):
                 pb.allreduce_()
         ms, _ = timed(step, reps, 2)
         ms /= reps
+        # the film as the last timed frame left it, i.e. AFTER the exchange: taken before the render-only loops
+        # below overwrite it with this rank's partial film
+        torch.cuda.synchronize()
+        mean_radiance = [float(x) for x in film[..., :3].mean(dim=(0, 1))]
+        share = [float(film[..., 3].min()), float(film[..., 3].max())]
+        film_check = {"verdict": "n/a (1 GPU: nothing exchanged)"}
+        if comm is not None:
+            # this rank alone renders ALL sample indices of the same seed; the exchanged film must equal it up to
+            # the order of the float additions
+            solo = torch.zeros(h, w, 4, device=dev)
+            RD.render(sc, w, h, spp, max_depth=depth, seed=1, film=solo)
+            torch.cuda.synchronize()
+            num = float(((film[..., :3] - solo[..., :3]) ** 2).mean())
+            den = float((solo[..., :3] ** 2).mean())
+            rel = num / max(den, 1e-30)
+            film_check = {"rel_mse_exchanged_vs_one_gpu_render": rel, "bar": 1e-6, "verdict": "ok" if rel <= 1e-6 else "FAILED"}
+            del solo
         per_rank = None
         if comm is not None:
             # each rank's own render time, no exchange and no barrier in the loop: is the frame time the slowest
@@ -689,8 +788,7 @@ def render_legs(plug, world, rank, local, comm, timed, ntab):
         out[name] = {"width": w, "height": h, "spp": spp, "max_depth": depth, "ms": ms,
                      "render_only_ms_per_rank": per_rank,
                      "spp_mpix_per_s": spp * w * h / 1e6 / (ms * 1e-3),
-                     "mean_radiance": [float(x) for x in film[..., :3].mean(dim=(0, 1))],
-                     "sample_share_min_max": [float(film[..., 3].min()), float(film[..., 3].max())],
+                     "mean_radiance": mean_radiance, "sample_share_min_max": share, "film_check": film_check,
                      "film_exchange": "peer-memory kernel" if pb is not None else "none (1 GPU)"}
         del film
         if pb is not None:

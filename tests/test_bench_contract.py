@@ -61,3 +61,8 @@ def test_cpu_legs_subprocess_reports_config1(built_lib):
     assert one["threads"] == 1 and all_["threads"] == c["cores"] and c["config1_2p20"]["pairs"] == 1 << 20
     for leg in (one, all_):
         assert leg["eval_pdf_gquery_s"] > 0 and leg["sample_gquery_s"] > 0
+    # the render half of the metric (spp*Mpix/s) has its CPU figure too: configs 2 and 5 through the render oracle
+    r = c["render"]
+    assert r["cfg2_all_threads"]["spp_mpix_per_s"] > 0 and r["cfg2_all_threads"]["threads"] == c["cores"]
+    assert r["cfg2_single_thread"]["threads"] == 1 and r["cfg5_all_threads"]["spp_mpix_per_s"] > 0
+    assert (r["cfg5_all_threads"]["width"], r["cfg5_all_threads"]["height"]) == (1024, 1024)
