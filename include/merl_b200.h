@@ -301,7 +301,7 @@ int merl_allreduce_sum_f32(merl_comm_t* c, float* buf, int64_t count, merl_strea
  *     NVSwitch); merl_peerbuf_allreduce is this library's own kernel: rank r reads slab r with
  *     multimem.ld_reduce (the switch adds the R copies), applies the mask, writes it back to all R
  *     copies with multimem.st; multicast flag barriers.  MERL_ERR_UNSUPPORTED when the build had no
- *     NCCL device headers, the loaded NCCL differs from them, or there is no multicast over all ranks
+ *     NCCL device headers, the loaded NCCL is not exactly the release of those headers, or there is no multicast over all ranks
  *     (every rank gets the same answer, so a host can fall back to another transport collectively).
  * merl_peerbuf_allreduce(count = floats to sum, multiple of 4; mask_table = NULL or the table whose
  * gradient this is, then count must be 4 * ncell) is asynchronous on `stream`; every rank must call it

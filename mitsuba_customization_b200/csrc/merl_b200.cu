@@ -1448,9 +1448,13 @@ static int merl_peerbuf_create_impl(merl_comm_t* c, int64_t count, int transport
             return bail(fail(MERL_ERR_UNSUPPORTED, "the loaded NCCL has no symmetric windows / device communicators (needs 2.28+)"));
         int v = 0;
         if (a->GetVersion) a->GetVersion(&v);
-        if (v / 100 != NCCL_VERSION_CODE / 100)
-            return bail(fail(MERL_ERR_UNSUPPORTED, "built against NCCL %d headers, running NCCL %d: device structures may differ",
-                             NCCL_VERSION_CODE, v));
+        // EXACT match, patch level included: the multicast address below is assembled from NCCL's device-side
+        // structures (ncclWindow_vidmem, ncclDevComm) as the headers of the build lay them out, and those are
+        // private to a release.  With any other library a wrong pointer would make multimem.st write into
+        // arbitrary peer memory without an error, so the host falls back to another transport instead.
+        if (v != NCCL_VERSION_CODE)
+            return bail(fail(MERL_ERR_UNSUPPORTED, "built against NCCL %d headers, running NCCL %d: the device structures the NVLS "
+                             "transport reads are private to a release, an exact match is required", NCCL_VERSION_CODE, v));
         const size_t data_bytes = (bytes + 4095) & ~(size_t)4095, flag_bytes = sizeof(uint32_t) * 2 * kXchgMaxCtas;
         if (a->MemAlloc((void**)&b->d_buf, data_bytes + flag_bytes) != 0 || !b->d_buf) {
             b->d_buf = nullptr;
@@ -2076,6 +2080,12 @@ static int merl_render_impl(const merl_table_t* const* tables, int ntables, cons
         RT_TRY(cudaMemcpyAsync(&nq, d_nq, 8, cudaMemcpyDeviceToHost, s));
         RT_TRY(cudaStreamSynchronize(s));
         stats_out->paths = total; stats_out->bsdf_queries = (int64_t)nq; stats_out->launches = launches;
+        // by-table mode: the frame's per-bounce exchanges have run by now; one that timed out left the stage
+        // outputs of its pass unsummed (the kernel skips the data phase), so the film is not to be used
+        if (own_world > 1 && p->stage_exchange->h_status && *reinterpret_cast<volatile int*>(p->stage_exchange->h_status)) {
+            rc = fail(MERL_ERR_CUDA, "a stage exchange of this frame timed out waiting for another rank; the film is incomplete");
+            goto done;
+        }
     }
     }
 done:

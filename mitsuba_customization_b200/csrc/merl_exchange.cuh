@@ -74,10 +74,14 @@ __device__ __forceinline__ void st_peer(float4* p, const float4 v) {
 #ifndef MERL_XCHG_THREAD_FENCE
 #define MERL_XCHG_THREAD_FENCE 0
 #endif
-__device__ __forceinline__ void xchg_barrier(const PeerView& pv, const int cta, const uint32_t epoch, int* status) {
+// Returns false (to every thread of the CTA) when a wait ran into the timeout: the peers' data cannot be
+// trusted then, and the callers skip their data phase instead of summing unsynchronised buffers.
+__device__ __forceinline__ bool xchg_barrier(const PeerView& pv, const int cta, const uint32_t epoch, int* status) {
+    __shared__ int timed_out;
 #if MERL_XCHG_THREAD_FENCE
     __threadfence_system();
 #endif
+    if (threadIdx.x == 0) timed_out = 0;
     __syncthreads();
     if ((int)threadIdx.x < pv.nranks) {
         const int p = threadIdx.x;
@@ -85,10 +89,17 @@ __device__ __forceinline__ void xchg_barrier(const PeerView& pv, const int cta, 
         const uint32_t* mine = pv.flags[pv.rank] + cta * kMaxRanks + p;
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-            if (clock64() - t0 > kXchgTimeoutCycles) { *reinterpret_cast<volatile int*>(status) = 1; break; }   // host-mapped word
+            if (clock64() - t0 > kXchgTimeoutCycles) {
+                *reinterpret_cast<volatile int*>(status) = 1;   // host-mapped word
+                timed_out = 1;
+                break;
+            }
         }
     }
     __syncthreads();
+    const bool ok = timed_out == 0;
+    __syncthreads();   // everyone has read the flag before the next barrier call resets it
+    return ok;
 }
 
 __device__ __forceinline__ float4 mask_cell(float4 g, const float bits) {
@@ -112,9 +123,9 @@ __global__ void __launch_bounds__(kXchgThreads) peer_allreduce_kernel(const Peer
     __syncthreads();
     const uint32_t e0 = e_s;
     const int R = NR > 0 ? NR : pv.nranks;
-    xchg_barrier(pv, cta, e0 + 1u, status);
+    const bool peers_ready = xchg_barrier(pv, cta, e0 + 1u, status);
     const int64_t per = (n4 + R - 1) / R;
-    const int64_t lo = min((int64_t)pv.rank * per, n4), hi = min(lo + per, n4);
+    const int64_t lo = min((int64_t)pv.rank * per, n4), hi = peers_ready ? min(lo + per, n4) : lo;   // timeout: no data phase
     const int64_t step = (int64_t)gridDim.x * kXchgThreads;
     for (int64_t i0 = lo + (int64_t)cta * kXchgThreads + threadIdx.x; i0 < hi; i0 += step * UNROLL) {
         float4 acc[UNROLL];
@@ -196,16 +207,23 @@ struct NvlsView {
     uint32_t* epoch_words;    // this rank only: arrivals this CTA has already waited for
     int nranks, rank;
 };
-__device__ __forceinline__ void nvls_barrier(const NvlsView& nv, const int cta, const uint32_t target, int* status) {
+__device__ __forceinline__ bool nvls_barrier(const NvlsView& nv, const int cta, const uint32_t target, int* status) {
+    __shared__ int timed_out;
     __syncthreads();
     if (threadIdx.x == 0) {
+        timed_out = 0;
         asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(nv.mc_flags + cta), "r"(1u) : "memory");
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(nv.my_flags + cta) - target) < 0) {
-            if (clock64() - t0 > kXchgTimeoutCycles) { *reinterpret_cast<volatile int*>(status) = 1; break; }
+            if (clock64() - t0 > kXchgTimeoutCycles) {
+                *reinterpret_cast<volatile int*>(status) = 1;
+                timed_out = 1;
+                break;
+            }
         }
     }
     __syncthreads();
+    return timed_out == 0;   // thread 0 alone writes the flag, and only after the next call's first __syncthreads
 }
 template <int UNROLL>
 __global__ void __launch_bounds__(kXchgThreads) nvls_allreduce_kernel(const NvlsView nv, const int64_t n4,
@@ -217,9 +235,9 @@ __global__ void __launch_bounds__(kXchgThreads) nvls_allreduce_kernel(const Nvls
     __syncthreads();
     const uint32_t e0 = e_s;
     const uint32_t R = (uint32_t)nv.nranks;
-    nvls_barrier(nv, cta, e0 + R, status);
+    const bool peers_ready = nvls_barrier(nv, cta, e0 + R, status);
     const int64_t per = (n4 + R - 1) / R;
-    const int64_t lo = min((int64_t)nv.rank * per, n4), hi = min(lo + per, n4);
+    const int64_t lo = min((int64_t)nv.rank * per, n4), hi = peers_ready ? min(lo + per, n4) : lo;   // timeout: no data phase
     const int64_t step = (int64_t)gridDim.x * kXchgThreads;
     for (int64_t i0 = lo + (int64_t)cta * kXchgThreads + threadIdx.x; i0 < hi; i0 += step * UNROLL) {
         float4 acc[UNROLL];
