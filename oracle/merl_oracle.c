@@ -171,6 +171,56 @@ void orc_bins(const orc_table_t *t, const float *wix, const float *wiy, const fl
     }
 }
 
+/* Single-precision twin of bins_from_dirs: every step of SURVEY.md App. A (half vector, acos/atan2,
+ * the two Rodrigues rotations, the three index formulas) carried out in `float` with the float libm,
+ * as a Mitsuba 3 non-double variant (scalar_rgb, llvm_rgb, cuda_rgb: Float = float) would compute it
+ * if the fork's plugin is a straight port of the public reader.  It is NOT
+ * what libmerl_b200 matches -- that is the double path above -- it exists to MEASURE how often the two
+ * precisions land in different cells, i.e. how much of "bit-exact bins" hinges on assumption B1. */
+static void rotate_about_f(const float v[3], const float axis[3], float angle, float out[3]) {
+    const float c = cosf(angle), s = sinf(angle);
+    const float k = (axis[0] * v[0] + axis[1] * v[1] + axis[2] * v[2]) * (1.0f - c);
+    const float cr[3] = {axis[1] * v[2] - axis[2] * v[1], axis[2] * v[0] - axis[0] * v[2],
+                         axis[0] * v[1] - axis[1] * v[0]};
+    for (int a = 0; a < 3; ++a) out[a] = v[a] * c + axis[a] * k + cr[a] * s;
+}
+static int bins_from_dirs_f32(const orc_table_t *t, const float in[3], const float out[3]) {
+    const float PI_F = (float)M_PI;
+    float h[3] = {in[0] + out[0], in[1] + out[1], in[2] + out[2]};
+    const float len = sqrtf(h[0] * h[0] + h[1] * h[1] + h[2] * h[2]);
+    if (len > 0.0f) { h[0] /= len; h[1] /= len; h[2] /= len; }
+    const float hz = h[2] > 1.0f ? 1.0f : (h[2] < -1.0f ? -1.0f : h[2]);
+    const float theta_half = acosf(hz), fi_half = atan2f(h[1], h[0]);
+    static const float normal[3] = {0.0f, 0.0f, 1.0f}, binormal[3] = {0.0f, 1.0f, 0.0f};
+    float tmp[3], d[3];
+    rotate_about_f(in, normal, -fi_half, tmp);
+    rotate_about_f(tmp, binormal, -theta_half, d);
+    const float dz = d[2] > 1.0f ? 1.0f : (d[2] < -1.0f ? -1.0f : d[2]);
+    const float theta_diff = acosf(dz);
+    float fi_diff = atan2f(d[1], d[0]);
+    int ih, id, ip;
+    if (theta_half <= 0.0f) ih = 0;
+    else {
+        float x = theta_half / (PI_F / 2.0f) * (float)t->nh;
+        if (t->theta_h_sqrt) x = sqrtf(x * (float)t->nh);
+        ih = (int)x; if (ih < 0) ih = 0; if (ih >= t->nh) ih = t->nh - 1;
+    }
+    id = (int)(theta_diff / (PI_F * 0.5f) * (float)t->nd);
+    id = id < 0 ? 0 : (id < t->nd - 1 ? id : t->nd - 1);
+    if (fi_diff < 0.0f) fi_diff += PI_F;
+    ip = (int)(fi_diff / PI_F * (float)(2 * t->np) / 2.0f);
+    ip = ip < 0 ? 0 : (ip < t->np - 1 ? ip : t->np - 1);
+    return flat_index(t, ih, id, ip);
+}
+void orc_bins_f32(const orc_table_t *t, const float *wix, const float *wiy, const float *wiz,
+                  const float *wox, const float *woy, const float *woz, int64_t n, int32_t *idx) {
+#pragma omp parallel for schedule(static)
+    for (int64_t q = 0; q < n; ++q) {
+        const float in[3] = {wix[q], wiy[q], wiz[q]}, out[3] = {wox[q], woy[q], woz[q]};
+        idx[q] = bins_from_dirs_f32(t, in, out);
+    }
+}
+
 /* Table read + scale (public reader: lookup_brdf_val's tail). */
 static inline void cell_rgb(const orc_table_t *t, int idx, double rgb[3]) {
     const int64_t N = (int64_t)t->nh * t->nd * t->np;

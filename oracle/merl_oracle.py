@@ -119,6 +119,16 @@ class OracleTable:
         out["stable"] = stable.astype(bool)
         return out
 
+    def bins_f32(self, wi, wo):
+        """Flat cell index from the all-float twin of the binning (what a float variant of a straight port of the
+        public reader would compute): for measuring the double <-> float disagreement, not a parity target."""
+        wi, wo = _dirs(wi), _dirs(wo)
+        n = wi.shape[1]
+        idx = np.empty(n, dtype=np.int32)
+        lib().orc_bins_f32(C.byref(self.t), _p(wi[0]), _p(wi[1]), _p(wi[2]), _p(wo[0]), _p(wo[1]), _p(wo[2]),
+                           C.c_int64(n), _p(idx))
+        return idx
+
     def eval_pdf(self, wi, wo, want_pdf=True):
         if want_pdf and self.cdf is None:
             # the C side would return the cosine lobe's share only: a silently incomplete density
