@@ -282,6 +282,19 @@ template <typename K> static int blocks_per_sm(K kernel, size_t smem) {
 
 // Persistent launch: grid = min(work, SMs x resident CTAs), with the table's persisting-L2
 // access window attached to the launch itself (no mutation of the caller's stream).
+// The window normally covers the table's cells.  A launch that never reads them (the unmasked scatter of
+// merl_backward) sets tl_window_base to its own L2-resident working set -- the gradient table -- for the
+// duration of the launch call; nullptr = the cells.
+static thread_local const void* tl_window_base = nullptr;
+struct WindowOverride {
+    explicit WindowOverride(const void* p) { tl_window_base = p; }
+    ~WindowOverride() { tl_window_base = nullptr; }
+};
+static bool pin_gradient_window() {
+    static const bool on = [] { const char* e = getenv("MERL_BWD_PIN_GRAD"); return !e || atoi(e) != 0; }();
+    return on;
+}
+
 template <typename K, typename... Args>
 static int launch_persistent(const merl_table* t, K kernel, size_t smem, int64_t items, cudaStream_t stream,
                              Args... args) {
@@ -296,7 +309,7 @@ static int launch_persistent(const merl_table* t, K kernel, size_t smem, int64_t
     cudaLaunchAttribute attr[1];
     if (t->persist_bytes) {
         attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
-        attr[0].val.accessPolicyWindow.base_ptr = (void*)t->d_cells;
+        attr[0].val.accessPolicyWindow.base_ptr = tl_window_base ? const_cast<void*>(tl_window_base) : (void*)t->d_cells;
         attr[0].val.accessPolicyWindow.num_bytes = t->persist_bytes;
         attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
         attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
@@ -896,6 +909,8 @@ static int run_backward(const merl_table* t, BackwardIn in, int64_t n, float4* g
                      aligned(q.woy, 16) && aligned(q.woz, 16) && aligned(q.active, 4) && aligned(in.gr, 16) &&
                      aligned(in.gg, 16) && aligned(in.gb, 16);
     int64_t done = 0;
+    // GATHER == 0 never reads the cells: the persisting window goes to the gradient table (same size) instead
+    WindowOverride win(!GATHER && pin_gradient_window() ? (const void*)grad : nullptr);
     if (vec && n >= 4) {
         using Op = BackwardOp<4, AGG, GATHER, CTA>;
         const int rc = launch_op<Op, MERL_BWD_MINB>(t, Op{in.q, in.gr, in.gg, in.gb, grad, extra_smem_offset<Op>(fl)}, fl, n / 4, s);
